@@ -1,0 +1,229 @@
+/* shellac_b200.h — C ABI of libshellac_b200.so
+ *
+ * The B200-native replacement for the one data-parallel hot path of kmacrow/Shellac:
+ * batched HTTP/1.1 message tokenising + body framing (reference: HttpParser.py:140-337),
+ * cache key = request URL verbatim (reference: Server.py:327) and ketama/MD5 placement of each
+ * key on a memcached continuum (reference: pylibmc.Client(..., behaviors={'ketama': True}),
+ * Server.py:81-83, called at Server.py:335 and :432; arithmetic = libmemcached 0.44, not vendored).
+ *
+ * Plain C: pointers and sizes only.  Bind it with ctypes the way the
+ * reference binds libmemcached through pylibmc.  Every entry point returns 0 on success and a
+ * negative SHL_ERR_* on a library/CUDA failure (text via shl_last_error).  Per-message parse
+ * outcomes are DATA (the `status` word), not errors: the Python facade raises the matching
+ * exception type at the call at which the reference would have raised.
+ *
+ * Threading: one ctx per GPU; a ctx is not thread-safe (same contract as HttpParser.py:21).
+ * All work is queued on the ctx's stream and is asynchronous until shl_sync().
+ */
+#ifndef SHELLAC_B200_H
+#define SHELLAC_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------------------------------
+ * Library return codes
+ * ---------------------------------------------------------------------------------------- */
+#define SHL_OK              0
+#define SHL_ERR_CUDA       -1   /* a CUDA runtime call failed; see shl_last_error()            */
+#define SHL_ERR_ARG        -2   /* bad argument (null pointer, size beyond the ctx capacity)   */
+#define SHL_ERR_NO_RING    -3   /* placement requested before shl_ring_build()                 */
+#define SHL_ERR_NO_DEVICE  -4   /* no CUDA device: there is no CPU fallback, by design         */
+#define SHL_ERR_CAPACITY   -5   /* header/chunk record arena overflowed (raise max_records)    */
+
+/* ------------------------------------------------------------------------------------------
+ * Per-message status word  (u32):  bits 0..7 = outcome code, bits 8.. = flags
+ *
+ * The outcome codes follow the exception taxonomy of the reference parser
+ * (HttpParser.py:304-337, 194-200, 234-241); "INCOMPLETE_*" are the states in which the
+ * reference's parse() returns `length` and waits for more bytes (HttpParser.py:156-157,
+ * 177-178, 208-211, 255-256, 286-287, 291-294).
+ * ---------------------------------------------------------------------------------------- */
+enum {
+    SHL_S_OK                 = 0,  /* message_complete() is True                                   */
+    SHL_S_EMPTY              = 1,  /* length == 0: parse() returns None       (HttpParser.py:143)  */
+    SHL_S_INCOMPLETE_LINE    = 2,  /* no CRLF yet                             (HttpParser.py:155)  */
+    SHL_S_INCOMPLETE_HEADERS = 3,  /* no CRLFCRLF after the first line        (HttpParser.py:176)  */
+    SHL_S_INCOMPLETE_BODY    = 4,  /* headers done, body/chunks not all here  (HttpParser.py:208,291) */
+    SHL_E_FIRSTLINE_PARTS    = 16, /* ValueError: rstrip().split(' ',2) != 3 parts (HttpParser.py:307) */
+    SHL_E_VERSION_SPLIT      = 17, /* ValueError: split('/') != 2 parts        (HttpParser.py:311,318) */
+    SHL_E_VERSION_FLOAT      = 18, /* ValueError: float(version)               (HttpParser.py:312,319) */
+    SHL_E_STATUS_INT         = 19, /* ValueError: int(status)                  (HttpParser.py:313) */
+    SHL_E_HDR_NO_SEP         = 20, /* ValueError: header line without ": "     (HttpParser.py:328) */
+    SHL_E_HDR_MULTI_SEP      = 21, /* ValueError: header line with >= 2 ": "   (HttpParser.py:328) */
+    SHL_E_CLEN_INT           = 22, /* ValueError: int(content-length)          (HttpParser.py:197) */
+    SHL_E_CLEN_LIST          = 23, /* TypeError : duplicate content-length -> int(list) (HttpParser.py:197) */
+    SHL_E_CHUNK_HEX          = 24, /* ValueError: int(chunk-size, 16)          (HttpParser.py:239,241) */
+    SHL_E_LIB_HDR_TOO_LARGE  = 32, /* library limit: header block ends beyond byte 65535 of the message */
+    SHL_E_LIB_RECORDS_FULL   = 33  /* library limit: the header/chunk record arena is full        */
+};
+#define SHL_CODE(st)             ((st) & 0xffu)
+#define SHL_F_IS_REQUEST         (1u << 8)   /* HttpParser.is_request()                            */
+#define SHL_F_HEADERS_COMPLETE   (1u << 9)   /* HttpParser.headers_complete()                      */
+#define SHL_F_MESSAGE_COMPLETE   (1u << 10)  /* HttpParser.message_complete()                      */
+#define SHL_F_ON_BODY            (1u << 11)  /* HttpParser._on_body                                */
+#define SHL_F_CHUNKED            (1u << 12)  /* HttpParser._chunked                                */
+#define SHL_F_VERSION_SHIFT      13          /* 2 bits: 0 = "1.0", 1 = "1.1", 2 = other valid float text, 3 = not parsed */
+#define SHL_F_VERSION_MASK       (3u << SHL_F_VERSION_SHIFT)
+#define SHL_F_STATUS_WIDE        (1u << 15)  /* int(status) valid but does not fit status_code: host converts the span */
+#define SHL_F_CLEN_WIDE          (1u << 16)  /* int(content-length) valid but beyond int64: host converts the span     */
+#define SHL_F_FIRST_LINE_DONE    (1u << 17)  /* _parse_first_line returned (fields below are valid)                   */
+
+/* One header line, offsets relative to the first byte of the message.
+ * key   = line[:sep]            (NOT stripped; the reference lower()s it, HttpParser.py:330)
+ * value = line[sep+2:].strip()  (py2 whitespace set {9..13, 32},     HttpParser.py:329)        */
+typedef struct shl_hdr_span {
+    uint16_t key_off, key_len, val_off, val_len;
+} shl_hdr_span;
+
+/* One chunk of a chunked body, offsets relative to the first byte of the message.
+ * [hdr_off, hdr_off+hdr_len) is what CHUNK_HEADER_RX matched (HttpParser.py:39-40,253-260),
+ * i.e. it includes the previous chunk's trailing CRLF; data follows immediately.
+ * One reference parse() call consumes hdr_len + data_len bytes (HttpParser.py:263,299).         */
+typedef struct shl_chunk_span {
+    uint32_t hdr_off, hdr_len, data_off, data_len;
+} shl_chunk_span;
+
+/* Struct-of-arrays parse result.  Every pointer addresses `n` elements (host memory for the
+ * *_batch entry points, device memory for the *_dev ones).  Offsets are relative to the message.
+ *   method = [0, sp1)   url = [sp1+1, sp2)   c = [sp2+1, fl_end)      (HttpParser.py:307)
+ *   request : version text = [slash+1, fl_end)                           (HttpParser.py:318-319)
+ *   response: version text = [slash+1, sp1), reason = c, status text = [sp1+1, sp2)  (:311-314)  */
+typedef struct shl_parse_out {
+    uint32_t* status;          /* code | flags                                                     */
+    uint32_t* first_line_len;  /* nb_parsed of the first parse() call = idx+2 (HttpParser.py:163)   */
+    uint32_t* headers_len;     /* nb_parsed of the second parse() call    (HttpParser.py:184)       */
+    uint32_t* sp1;
+    uint32_t* sp2;
+    uint32_t* fl_end;          /* end of the rstrip()ped first line                                */
+    uint32_t* slash;           /* position of the '/' that split() used                            */
+    int32_t*  status_code;     /* int(b) for responses, 0 for requests                             */
+    uint32_t* n_headers;       /* header lines tokenised (lines before the offending one on error) */
+    uint32_t* hdr_base;        /* index of this message's first record in hdr[]                    */
+    int64_t*  content_len;     /* HttpParser._content_len after the header state (0 if chunked)    */
+    shl_hdr_span* hdr;         /* record arena, `hdr_cap` entries                                  */
+    uint64_t  hdr_cap;
+    uint64_t* hdr_used;        /* one element: records written                                     */
+} shl_parse_out;
+
+/* Chunked-body framing result (struct-of-arrays, n elements each). */
+typedef struct shl_frame_out {
+    uint32_t* fstatus;         /* SHL_S_OK / SHL_S_INCOMPLETE_BODY / SHL_E_CHUNK_HEX / 0xff = not chunked */
+    uint32_t* n_chunks;        /* data-carrying chunks (the terminating 0-chunk is not counted)     */
+    uint32_t* chunk_base;      /* index of the first record in chunk[]                              */
+    uint64_t* body_end;        /* message-relative offset one past the last byte parse() consumed   */
+    uint64_t* body_bytes;      /* sum of data_len = length of the de-chunked body                   */
+    uint32_t* last_call;       /* nb_parsed of the final parse() call (HttpParser.py:270,276,280)   */
+    shl_chunk_span* chunk;     /* record arena, `chunk_cap` entries                                 */
+    uint64_t  chunk_cap;
+    uint64_t* chunk_used;
+} shl_frame_out;
+
+/* Placement result (struct-of-arrays, n elements each). */
+typedef struct shl_place_out {
+    uint8_t*  md5;             /* 16 bytes per key: RFC 1321 digest (libhashkit md5.c)              */
+    uint32_t* hash;            /* LE32(md5[0:4])            (libhashkit hashkit_md5)               */
+    uint32_t* node;            /* server index in ring order (libmemcached hash.c dispatch_host)   */
+    uint64_t* hist;            /* n_nodes counters, ADDED to (caller zeroes); may be NULL          */
+} shl_place_out;
+
+/* Ring modes (libmemcached hosts.c update_continuum).                                           */
+#define SHL_RING_KETAMA           0  /* 'ketama': True -> 100 points/server, 1 MD5 per point: the reference's setting (Server.py:83) */
+#define SHL_RING_KETAMA_WEIGHTED  1  /* ketama_weighted -> 160 points/server, 4 points per MD5 (BASELINE config 4)                  */
+
+typedef struct shl_ctx shl_ctx;
+
+/* ------------------------------------------------------------------------------------------
+ * Context / memory.  Mirrors pylibmc.Client construction (Server.py:81-83): one object owns the
+ * device buffers, the stream and the ring.
+ * ---------------------------------------------------------------------------------------- */
+int  shl_device_count(void);
+int  shl_ctx_create(int device, uint64_t max_msgs, uint64_t max_bytes, uint64_t max_records, shl_ctx** out);
+void shl_ctx_destroy(shl_ctx* ctx);
+const char* shl_last_error(shl_ctx* ctx);           /* ctx may be NULL: last error of ctx creation */
+int  shl_sync(shl_ctx* ctx);
+int  shl_pinned_alloc(void** ptr, uint64_t bytes);  /* page-locked host memory for arenas/outputs  */
+int  shl_pinned_free(void* ptr);
+int  shl_device_alloc(shl_ctx* ctx, void** dptr, uint64_t bytes);
+int  shl_device_free(shl_ctx* ctx, void* dptr);
+int  shl_memcpy_h2d(shl_ctx* ctx, void* dst, const void* src, uint64_t bytes);   /* async on the ctx stream */
+int  shl_memcpy_d2h(shl_ctx* ctx, void* dst, const void* src, uint64_t bytes);
+int  shl_memset_dev(shl_ctx* ctx, void* dst, int value, uint64_t bytes);
+/* Device-side timing on the ctx stream (CUDA events). slot in [0,16). */
+int  shl_event_record(shl_ctx* ctx, int slot);
+int  shl_event_elapsed_ms(shl_ctx* ctx, int slot_start, int slot_stop, float* ms);
+/* Stream handle (cudaStream_t) so a caller can order other work (e.g. an NCCL all-reduce) after ours. */
+void* shl_stream(shl_ctx* ctx);
+
+/* ------------------------------------------------------------------------------------------
+ * Ring.  Replaces libmemcached's update_continuum (hosts.c) behind pylibmc.Client(servers, ...)
+ * (Server.py:81-83).  hosts[i]/ports[i] are the '%s:%d' pieces in CLI order (Server.py:81,493-505);
+ * weights may be NULL (all 1).  Host index = list position.
+ * ---------------------------------------------------------------------------------------- */
+int  shl_ring_build(shl_ctx* ctx, const char* const* hosts, const uint32_t* ports,
+                    const uint32_t* weights, uint32_t n_hosts, int mode);
+int  shl_ring_size(shl_ctx* ctx, uint32_t* n_points, uint32_t* n_hosts);
+int  shl_ring_export(shl_ctx* ctx, uint32_t* values, uint32_t* nodes, uint32_t cap);
+
+/* ------------------------------------------------------------------------------------------
+ * Host-buffer entry points (the drop-in boundary).  Inputs and outputs are HOST pointers
+ * (pinned for full speed); each call copies H2D, runs the kernels, copies D2H, all on the ctx
+ * stream; results are valid after shl_sync().
+ *
+ * shl_parse_batch  replaces  HttpParser.parse() driven to completion over each message
+ *                  (HttpParser.py:140-202, 304-337; caller loop Server.py:320-325).
+ * shl_frame_batch  replaces  HttpParser._parse_chunked / Content-Length framing
+ *                  (HttpParser.py:204-301) for the messages shl_parse_batch flagged.
+ * shl_place_batch  replaces  the placement inside pylibmc get/set (Server.py:335,432).
+ * shl_route_batch  = parse + (key = url(), Server.py:327) + place, fused on the device: the
+ *                  request path of Server._read_requests (Server.py:320-335).
+ * ---------------------------------------------------------------------------------------- */
+int  shl_parse_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes,
+                     const uint64_t* off, const uint32_t* len, uint64_t n, const shl_parse_out* out);
+int  shl_frame_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes,
+                     const uint64_t* off, const uint32_t* len, uint64_t n,
+                     const uint32_t* status, const uint32_t* first_line_len, const uint32_t* headers_len,
+                     const shl_frame_out* out);
+int  shl_place_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes,
+                     const uint64_t* key_off, const uint32_t* key_len, uint64_t n, const shl_place_out* out);
+int  shl_route_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes,
+                     const uint64_t* off, const uint32_t* len, uint64_t n,
+                     const shl_parse_out* pout, const shl_place_out* qout);
+
+/* ------------------------------------------------------------------------------------------
+ * Device-resident entry points: same semantics, every data pointer is a DEVICE pointer and no
+ * copy is made.  For callers whose arenas already live in HBM, and for kernel-only timing.
+ * ---------------------------------------------------------------------------------------- */
+int  shl_parse_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_off, const uint32_t* d_len,
+                   uint64_t n, const shl_parse_out* d_out);
+int  shl_frame_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_off, const uint32_t* d_len,
+                   uint64_t n, const uint32_t* d_status, const uint32_t* d_first_line_len,
+                   const uint32_t* d_headers_len, const shl_frame_out* d_out);
+int  shl_place_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_key_off, const uint32_t* d_key_len,
+                   uint64_t n, const shl_place_out* d_out);
+int  shl_route_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_off, const uint32_t* d_len,
+                   uint64_t n, const shl_parse_out* d_pout, const shl_place_out* d_qout);
+
+/* Number of kernel launches this ctx has issued (for bench.py's gpu_launches claim). */
+uint64_t shl_launch_count(shl_ctx* ctx);
+
+/* ------------------------------------------------------------------------------------------
+ * Synthetic corpora (BASELINE.json configs 2-5; recipe in SURVEY.md section 8d).  A counter-based
+ * generator: message i is a pure function of (seed, i), so the host and device versions produce
+ * identical bytes.  shl_corpus_lengths fills len[i]; the caller prefix-sums them into off[] and
+ * shl_corpus_fill_* writes the bytes.  kind: 0 = GET requests (config 2/4), 1 = keys only (config 5).
+ * ---------------------------------------------------------------------------------------- */
+int  shl_corpus_lengths_host(uint64_t seed, uint64_t first, uint64_t n, int kind, uint32_t* len);
+int  shl_corpus_fill_host(uint64_t seed, uint64_t first, uint64_t n, int kind,
+                          const uint64_t* off, uint8_t* arena);
+int  shl_corpus_lengths_dev(shl_ctx* ctx, uint64_t seed, uint64_t first, uint64_t n, int kind, uint32_t* d_len);
+int  shl_corpus_fill_dev(shl_ctx* ctx, uint64_t seed, uint64_t first, uint64_t n, int kind,
+                         const uint64_t* d_off, uint8_t* d_arena);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SHELLAC_B200_H */
