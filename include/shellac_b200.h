@@ -151,6 +151,7 @@ int  shl_device_alloc(shl_ctx* ctx, void** dptr, uint64_t bytes);
 int  shl_device_free(shl_ctx* ctx, void* dptr);
 int  shl_memcpy_h2d(shl_ctx* ctx, void* dst, const void* src, uint64_t bytes);   /* async on the ctx stream */
 int  shl_memcpy_d2h(shl_ctx* ctx, void* dst, const void* src, uint64_t bytes);
+int  shl_memcpy_d2d(shl_ctx* ctx, void* dst, const void* src, uint64_t bytes);
 int  shl_memset_dev(shl_ctx* ctx, void* dst, int value, uint64_t bytes);
 /* Device-side timing on the ctx stream (CUDA events). slot in [0,16). */
 int  shl_event_record(shl_ctx* ctx, int slot);
@@ -192,6 +193,14 @@ int  shl_place_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes,
 int  shl_route_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes,
                      const uint64_t* off, const uint32_t* len, uint64_t n,
                      const shl_parse_out* pout, const shl_place_out* qout);
+/* One CHUNK_HEADER_RX.match + _parse_chunk_size at the START of each window (HttpParser.py:253-261):
+ * hdr_len[i] = len(match.group()) or -1 when the regex does not match; size[i] = int(size, 16);
+ * ok[i] = 0 when that int() raises ValueError.  The primitive an incremental caller needs.       */
+int  shl_chunk_header_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes,
+                            const uint64_t* off, const uint32_t* len, uint64_t n,
+                            int32_t* hdr_len, uint64_t* size, uint8_t* ok);
+/* In every *_batch call `arena` may be NULL: the bytes uploaded by the previous *_batch call on
+ * this ctx are reused (parse, then frame the same arena, costs one H2D copy).                    */
 
 /* ------------------------------------------------------------------------------------------
  * Device-resident entry points: same semantics, every data pointer is a DEVICE pointer and no
@@ -209,6 +218,17 @@ int  shl_route_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_off, 
 
 /* Number of kernel launches this ctx has issued (for bench.py's gpu_launches claim). */
 uint64_t shl_launch_count(shl_ctx* ctx);
+
+/* Per-outcome counters: SHL_N_CODES bins indexed by SHL_CODE(status), accumulated on the device
+ * by every parse/route call (the "parse-error counts" that are all-reduced across GPUs next to
+ * the per-node placement histogram).  shl_code_hist copies them out (and optionally zeroes
+ * them); the *_dev getters expose the device buffers so a collective can read them in place.    */
+#define SHL_N_CODES 64
+int   shl_code_hist(shl_ctx* ctx, uint64_t* out, int reset);
+void* shl_code_hist_dev(shl_ctx* ctx);   /* uint64_t[SHL_N_CODES]                                  */
+void* shl_node_hist_dev(shl_ctx* ctx);   /* uint64_t[n_hosts], filled by *_batch calls with hist   */
+/* Test hook: route every message through the scalar (non-vectorised) device path. */
+int   shl_set_force_scalar(shl_ctx* ctx, int on);
 
 /* ------------------------------------------------------------------------------------------
  * Synthetic corpora (BASELINE.json configs 2-5; recipe in SURVEY.md section 8d).  A counter-based

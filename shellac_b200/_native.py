@@ -26,7 +26,7 @@ F_VERSION_SHIFT = 13
 F_STATUS_WIDE, F_CLEN_WIDE, F_FIRST_LINE_DONE = 1 << 15, 1 << 16, 1 << 17
 FS_NOT_CHUNKED = 0xff
 RING_KETAMA, RING_KETAMA_WEIGHTED = 0, 1
-N_CODES = 34          # histogram length for per-outcome counts
+N_CODES = 64          # SHL_N_CODES: histogram length for per-outcome counts
 
 CODE_NAMES = {
     0: 'OK', 1: 'EMPTY', 2: 'INCOMPLETE_LINE', 3: 'INCOMPLETE_HEADERS', 4: 'INCOMPLETE_BODY',
@@ -102,6 +102,7 @@ def lib():
         'shl_device_free': (i32, [vp, vp]),
         'shl_memcpy_h2d': (i32, [vp, vp, vp, u64]),
         'shl_memcpy_d2h': (i32, [vp, vp, vp, u64]),
+        'shl_memcpy_d2d': (i32, [vp, vp, vp, u64]),
         'shl_memset_dev': (i32, [vp, vp, i32, u64]),
         'shl_event_record': (i32, [vp, i32]),
         'shl_event_elapsed_ms': (i32, [vp, i32, i32, C.POINTER(C.c_float)]),
@@ -119,6 +120,10 @@ def lib():
         'shl_place_dev': (i32, [vp, vp, vp, vp, u64, C.POINTER(PlaceOutStruct)]),
         'shl_route_dev': (i32, [vp, vp, vp, vp, u64, C.POINTER(ParseOutStruct), C.POINTER(PlaceOutStruct)]),
         'shl_launch_count': (u64, [vp]),
+        'shl_code_hist': (i32, [vp, vp, i32]),
+        'shl_code_hist_dev': (vp, [vp]),
+        'shl_node_hist_dev': (vp, [vp]),
+        'shl_set_force_scalar': (i32, [vp, i32]),
         'shl_corpus_lengths_host': (i32, [u64, u64, u64, i32, vp]),
         'shl_corpus_fill_host': (i32, [u64, u64, u64, i32, vp, vp]),
         'shl_corpus_lengths_dev': (i32, [vp, u64, u64, u64, i32, vp]),

@@ -1,0 +1,551 @@
+// api.cu — the C ABI of libshellac_b200.so (declared in include/shellac_b200.h).
+//
+// Host side of the boundary: a context that owns the device arenas, the SoA output block, the
+// stream and the ketama ring; the H2D -> kernels -> D2H choreography of the *_batch entry points;
+// and the ring builder (libmemcached hosts.c update_continuum, restated).  No PyTorch, no CPU
+// parsing or hashing of request data: if CUDA is unavailable every entry point fails.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "parse_kernel.cuh"
+#include "frame_kernel.cuh"
+#include "corpus.cuh"
+
+namespace {
+
+std::string g_last_error;
+
+struct DevParse {             // device SoA block (one allocation)
+    shl_parse_out o{};
+    void* block = nullptr;
+};
+
+}  // namespace
+
+struct shl_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[16]{};
+    uint64_t max_msgs = 0, max_bytes = 0, max_records = 0;
+    uint8_t* d_arena = nullptr; uint64_t* d_off = nullptr; uint32_t* d_len = nullptr;
+    uint64_t* d_koff = nullptr; uint32_t* d_klen = nullptr;
+    shl_parse_out dp{}; shl_frame_out df{}; shl_place_out dq{};
+    uint64_t* d_counters = nullptr;       // [0]=hdr_used [1]=chunk_used [2..66)=code_hist
+    uint64_t* h_counters = nullptr;       // pinned mirror
+    int32_t* d_ch_len = nullptr; uint64_t* d_ch_size = nullptr; uint8_t* d_ch_ok = nullptr;
+    // ring
+    uint32_t* d_ring_values = nullptr; uint32_t* d_ring_nodes = nullptr;
+    std::vector<uint32_t> ring_values, ring_nodes;
+    uint32_t n_points = 0, n_hosts = 0;
+    uint64_t* d_hist = nullptr; uint32_t hist_cap = 0;
+    int force_scalar = 0;
+    uint64_t launches = 0;
+    std::string err;
+};
+
+namespace {
+
+int fail(shl_ctx* c, int code, const std::string& msg) {
+    if (c) c->err = msg;
+    g_last_error = msg;
+    return code;
+}
+#define CU(call)                                                                              \
+    do {                                                                                      \
+        cudaError_t e_ = (call);                                                              \
+        if (e_ != cudaSuccess)                                                                \
+            return fail(ctx, SHL_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+template <typename T>
+cudaError_t dalloc(T** p, uint64_t n) { return cudaMalloc(reinterpret_cast<void**>(p), std::max<uint64_t>(n, 1) * sizeof(T)); }
+
+// ---------------------------------------------------------------------------- host MD5 (ring labels only)
+struct Md5 {
+    static uint32_t rol(uint32_t x, int s) { return (x << s) | (x >> (32 - s)); }
+    static void block(uint32_t h[4], const uint8_t* p) {
+        static const uint32_t K[64] = {
+            0xd76aa478, 0xe8c7b756, 0x242070db, 0xc1bdceee, 0xf57c0faf, 0x4787c62a, 0xa8304613, 0xfd469501,
+            0x698098d8, 0x8b44f7af, 0xffff5bb1, 0x895cd7be, 0x6b901122, 0xfd987193, 0xa679438e, 0x49b40821,
+            0xf61e2562, 0xc040b340, 0x265e5a51, 0xe9b6c7aa, 0xd62f105d, 0x02441453, 0xd8a1e681, 0xe7d3fbc8,
+            0x21e1cde6, 0xc33707d6, 0xf4d50d87, 0x455a14ed, 0xa9e3e905, 0xfcefa3f8, 0x676f02d9, 0x8d2a4c8a,
+            0xfffa3942, 0x8771f681, 0x6d9d6122, 0xfde5380c, 0xa4beea44, 0x4bdecfa9, 0xf6bb4b60, 0xbebfbc70,
+            0x289b7ec6, 0xeaa127fa, 0xd4ef3085, 0x04881d05, 0xd9d4d039, 0xe6db99e5, 0x1fa27cf8, 0xc4ac5665,
+            0xf4292244, 0x432aff97, 0xab9423a7, 0xfc93a039, 0x655b59c3, 0x8f0ccc92, 0xffeff47d, 0x85845dd1,
+            0x6fa87e4f, 0xfe2ce6e0, 0xa3014314, 0x4e0811a1, 0xf7537e82, 0xbd3af235, 0x2ad7d2bb, 0xeb86d391};
+        static const int S[16] = {7, 12, 17, 22, 5, 9, 14, 20, 4, 11, 16, 23, 6, 10, 15, 21};
+        uint32_t w[16];
+        for (int i = 0; i < 16; i++) memcpy(&w[i], p + 4 * i, 4);
+        uint32_t a = h[0], b = h[1], c = h[2], d = h[3];
+        for (int i = 0; i < 64; i++) {
+            uint32_t f; int g;
+            switch (i >> 4) {
+                case 0: f = (b & c) | (~b & d); g = i; break;
+                case 1: f = (d & b) | (~d & c); g = (5 * i + 1) & 15; break;
+                case 2: f = b ^ c ^ d; g = (3 * i + 5) & 15; break;
+                default: f = c ^ (b | ~d); g = (7 * i) & 15; break;
+            }
+            const uint32_t t = a + f + K[i] + w[g];
+            a = d; d = c; c = b;
+            b += rol(t, S[(i >> 4) * 4 + (i & 3)]);
+        }
+        h[0] += a; h[1] += b; h[2] += c; h[3] += d;
+    }
+    static void digest(const std::string& s, uint32_t h[4]) {
+        h[0] = 0x67452301; h[1] = 0xefcdab89; h[2] = 0x98badcfe; h[3] = 0x10325476;
+        std::string m = s;
+        m.push_back((char)0x80);
+        while (m.size() % 64 != 56) m.push_back('\0');
+        const uint64_t bits = (uint64_t)s.size() * 8;
+        for (int k = 0; k < 8; k++) m.push_back((char)(bits >> (8 * k)));
+        for (size_t i = 0; i < m.size(); i += 64) block(h, reinterpret_cast<const uint8_t*>(m.data()) + i);
+    }
+};
+
+shl_parse_out slice_parse(void* block, uint64_t n, shl_hdr_span* hdr, uint64_t cap, uint64_t* used) {
+    // 12 arrays, each n elements, 8-byte aligned strides
+    uint8_t* p = static_cast<uint8_t*>(block);
+    const uint64_t s4 = (n * 4 + 15) & ~15ull, s8 = (n * 8 + 15) & ~15ull;
+    shl_parse_out o{};
+    o.status = (uint32_t*)p; p += s4; o.first_line_len = (uint32_t*)p; p += s4; o.headers_len = (uint32_t*)p; p += s4;
+    o.sp1 = (uint32_t*)p; p += s4; o.sp2 = (uint32_t*)p; p += s4; o.fl_end = (uint32_t*)p; p += s4;
+    o.slash = (uint32_t*)p; p += s4; o.status_code = (int32_t*)p; p += s4; o.n_headers = (uint32_t*)p; p += s4;
+    o.hdr_base = (uint32_t*)p; p += s4; o.content_len = (int64_t*)p; p += s8;
+    o.hdr = hdr; o.hdr_cap = cap; o.hdr_used = used;
+    return o;
+}
+uint64_t parse_block_bytes(uint64_t n) { return 10 * ((n * 4 + 15) & ~15ull) + ((n * 8 + 15) & ~15ull); }
+
+}  // namespace
+
+extern "C" {
+
+int shl_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+const char* shl_last_error(shl_ctx* ctx) { return ctx ? ctx->err.c_str() : g_last_error.c_str(); }
+
+int shl_ctx_create(int device, uint64_t max_msgs, uint64_t max_bytes, uint64_t max_records, shl_ctx** out) {
+    shl_ctx* ctx = nullptr;
+    if (!out) return fail(nullptr, SHL_ERR_ARG, "shl_ctx_create: out is null");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(nullptr, SHL_ERR_NO_DEVICE, "no CUDA device: libshellac_b200 has no CPU fallback");
+    if (device < 0 || device >= ndev) return fail(nullptr, SHL_ERR_ARG, "shl_ctx_create: bad device index");
+    ctx = new shl_ctx();
+    ctx->device = device;
+    ctx->max_msgs = std::max<uint64_t>(max_msgs, 1);
+    ctx->max_bytes = std::max<uint64_t>(max_bytes, 64);
+    ctx->max_records = max_records ? max_records : std::max<uint64_t>(ctx->max_bytes / 16, 1024);
+    CU(cudaSetDevice(device));
+    CU(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    for (auto& e : ctx->ev) CU(cudaEventCreate(&e));
+    const uint64_t n = ctx->max_msgs;
+    CU(dalloc(&ctx->d_arena, ctx->max_bytes + 64));
+    CU(dalloc(&ctx->d_off, n)); CU(dalloc(&ctx->d_len, n));
+    CU(dalloc(&ctx->d_koff, n)); CU(dalloc(&ctx->d_klen, n));
+    CU(dalloc(&ctx->d_counters, 66));
+    CU(cudaHostAlloc(reinterpret_cast<void**>(&ctx->h_counters), 66 * sizeof(uint64_t), cudaHostAllocDefault));
+    void* blk = nullptr;
+    CU(cudaMalloc(&blk, parse_block_bytes(n)));
+    shl_hdr_span* hdr = nullptr; CU(dalloc(&hdr, ctx->max_records));
+    ctx->dp = slice_parse(blk, n, hdr, ctx->max_records, ctx->d_counters + 0);
+    shl_frame_out& f = ctx->df;
+    CU(dalloc(&f.fstatus, n)); CU(dalloc(&f.n_chunks, n)); CU(dalloc(&f.chunk_base, n));
+    CU(dalloc(&f.body_end, n)); CU(dalloc(&f.body_bytes, n)); CU(dalloc(&f.last_call, n));
+    CU(dalloc(&f.chunk, ctx->max_records)); f.chunk_cap = ctx->max_records; f.chunk_used = ctx->d_counters + 1;
+    shl_place_out& q = ctx->dq;
+    CU(dalloc(&q.md5, 16 * n)); CU(dalloc(&q.hash, n)); CU(dalloc(&q.node, n));
+    CU(dalloc(&ctx->d_ch_len, n)); CU(dalloc(&ctx->d_ch_size, n)); CU(dalloc(&ctx->d_ch_ok, n));
+    CU(cudaFuncSetAttribute(shl::k_route<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
+    CU(cudaFuncSetAttribute(shl::k_route<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
+    const char* fs = getenv("SHL_FORCE_SCALAR");
+    ctx->force_scalar = (fs && fs[0] == '1') ? 1 : 0;
+    *out = ctx;
+    return SHL_OK;
+}
+
+void shl_ctx_destroy(shl_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(ctx->d_arena); cudaFree(ctx->d_off); cudaFree(ctx->d_len); cudaFree(ctx->d_koff); cudaFree(ctx->d_klen);
+    cudaFree(ctx->dp.status); cudaFree(ctx->dp.hdr);
+    cudaFree(ctx->df.fstatus); cudaFree(ctx->df.n_chunks); cudaFree(ctx->df.chunk_base); cudaFree(ctx->df.body_end);
+    cudaFree(ctx->df.body_bytes); cudaFree(ctx->df.last_call); cudaFree(ctx->df.chunk);
+    cudaFree(ctx->dq.md5); cudaFree(ctx->dq.hash); cudaFree(ctx->dq.node);
+    cudaFree(ctx->d_ch_len); cudaFree(ctx->d_ch_size); cudaFree(ctx->d_ch_ok);
+    cudaFree(ctx->d_counters); cudaFreeHost(ctx->h_counters);
+    cudaFree(ctx->d_ring_values); cudaFree(ctx->d_ring_nodes); cudaFree(ctx->d_hist);
+    for (auto& e : ctx->ev) cudaEventDestroy(e);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+int shl_sync(shl_ctx* ctx) {
+    if (!ctx) return SHL_ERR_ARG;
+    CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaGetLastError());
+    return SHL_OK;
+}
+
+int shl_pinned_alloc(void** ptr, uint64_t bytes) {
+    shl_ctx* ctx = nullptr;
+    if (!ptr) return SHL_ERR_ARG;
+    CU(cudaHostAlloc(ptr, std::max<uint64_t>(bytes, 1), cudaHostAllocDefault));
+    return SHL_OK;
+}
+int shl_pinned_free(void* ptr) { shl_ctx* ctx = nullptr; CU(cudaFreeHost(ptr)); return SHL_OK; }
+int shl_device_alloc(shl_ctx* ctx, void** dptr, uint64_t bytes) {
+    if (!ctx || !dptr) return SHL_ERR_ARG;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMalloc(dptr, std::max<uint64_t>(bytes, 1)));
+    return SHL_OK;
+}
+int shl_device_free(shl_ctx* ctx, void* dptr) { if (!ctx) return SHL_ERR_ARG; CU(cudaSetDevice(ctx->device)); CU(cudaFree(dptr)); return SHL_OK; }
+int shl_memcpy_h2d(shl_ctx* ctx, void* dst, const void* src, uint64_t bytes) {
+    if (!ctx) return SHL_ERR_ARG;
+    CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    return SHL_OK;
+}
+int shl_memcpy_d2h(shl_ctx* ctx, void* dst, const void* src, uint64_t bytes) {
+    if (!ctx) return SHL_ERR_ARG;
+    CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    return SHL_OK;
+}
+int shl_memcpy_d2d(shl_ctx* ctx, void* dst, const void* src, uint64_t bytes) {
+    if (!ctx) return SHL_ERR_ARG;
+    CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, ctx->stream));
+    return SHL_OK;
+}
+int shl_memset_dev(shl_ctx* ctx, void* dst, int value, uint64_t bytes) {
+    if (!ctx) return SHL_ERR_ARG;
+    CU(cudaMemsetAsync(dst, value, bytes, ctx->stream));
+    return SHL_OK;
+}
+int shl_event_record(shl_ctx* ctx, int slot) {
+    if (!ctx || slot < 0 || slot >= 16) return SHL_ERR_ARG;
+    CU(cudaEventRecord(ctx->ev[slot], ctx->stream));
+    return SHL_OK;
+}
+int shl_event_elapsed_ms(shl_ctx* ctx, int a, int b, float* ms) {
+    if (!ctx || !ms || a < 0 || a >= 16 || b < 0 || b >= 16) return SHL_ERR_ARG;
+    CU(cudaEventSynchronize(ctx->ev[b]));
+    CU(cudaEventElapsedTime(ms, ctx->ev[a], ctx->ev[b]));
+    return SHL_OK;
+}
+void* shl_stream(shl_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+uint64_t shl_launch_count(shl_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+// ------------------------------------------------------------------------------------ ring
+// libmemcached 0.44 hosts.c update_continuum, restated (PARITY UNPINNED: see DESIGN.md).
+int shl_ring_build(shl_ctx* ctx, const char* const* hosts, const uint32_t* ports, const uint32_t* weights,
+                   uint32_t n_hosts, int mode) {
+    if (!ctx || !hosts || !ports || n_hosts == 0) return fail(ctx, SHL_ERR_ARG, "shl_ring_build: bad argument");
+    struct Pt { uint32_t value, node; };
+    std::vector<Pt> pts;
+    pts.reserve((size_t)n_hosts * 160);
+    uint64_t W = 0;
+    for (uint32_t s = 0; s < n_hosts; s++) W += weights ? weights[s] : 1;
+    for (uint32_t s = 0; s < n_hosts; s++) {
+        uint32_t reps = 100, per = 1;                                   // MEMCACHED_POINTS_PER_SERVER
+        if (mode == SHL_RING_KETAMA_WEIGHTED) {                         // MEMCACHED_POINTS_PER_SERVER_KETAMA = 160
+            const float pct = (float)(weights ? weights[s] : 1) / (float)W;
+            float t = pct * 160;
+            t = t / 4;
+            t = t * (float)n_hosts;
+            reps = (uint32_t)floorf((float)((double)t + 0.0000000001));
+            per = 4;
+        }
+        for (uint32_t i = 0; i < reps; i++) {
+            char label[400];
+            int ln;
+            if (ports[s] == 11211) ln = snprintf(label, sizeof label, "%s-%u", hosts[s], i);
+            else ln = snprintf(label, sizeof label, "%s:%u-%u", hosts[s], ports[s], i);
+            uint32_t h[4];
+            Md5::digest(std::string(label, (size_t)ln), h);
+            for (uint32_t k = 0; k < per; k++) pts.push_back({h[k], s});
+        }
+    }
+    // value-only comparator; equal values keep insertion order (lower server index first)
+    std::stable_sort(pts.begin(), pts.end(), [](const Pt& a, const Pt& b) { return a.value < b.value; });
+    ctx->ring_values.resize(pts.size()); ctx->ring_nodes.resize(pts.size());
+    for (size_t i = 0; i < pts.size(); i++) { ctx->ring_values[i] = pts[i].value; ctx->ring_nodes[i] = pts[i].node; }
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    cudaFree(ctx->d_ring_values); cudaFree(ctx->d_ring_nodes);
+    ctx->d_ring_values = ctx->d_ring_nodes = nullptr;
+    CU(dalloc(&ctx->d_ring_values, pts.size())); CU(dalloc(&ctx->d_ring_nodes, pts.size()));
+    CU(cudaMemcpy(ctx->d_ring_values, ctx->ring_values.data(), pts.size() * 4, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(ctx->d_ring_nodes, ctx->ring_nodes.data(), pts.size() * 4, cudaMemcpyHostToDevice));
+    ctx->n_points = (uint32_t)pts.size(); ctx->n_hosts = n_hosts;
+    if (ctx->hist_cap < n_hosts) {
+        cudaFree(ctx->d_hist); ctx->d_hist = nullptr;
+        CU(dalloc(&ctx->d_hist, n_hosts));
+        ctx->hist_cap = n_hosts;
+    }
+    return SHL_OK;
+}
+int shl_ring_size(shl_ctx* ctx, uint32_t* n_points, uint32_t* n_hosts) {
+    if (!ctx) return SHL_ERR_ARG;
+    if (n_points) *n_points = ctx->n_points;
+    if (n_hosts) *n_hosts = ctx->n_hosts;
+    return SHL_OK;
+}
+int shl_ring_export(shl_ctx* ctx, uint32_t* values, uint32_t* nodes, uint32_t cap) {
+    if (!ctx || cap < ctx->n_points) return fail(ctx, SHL_ERR_ARG, "shl_ring_export: capacity too small");
+    if (values) memcpy(values, ctx->ring_values.data(), (size_t)ctx->n_points * 4);
+    if (nodes) memcpy(nodes, ctx->ring_nodes.data(), (size_t)ctx->n_points * 4);
+    return SHL_OK;
+}
+
+// ------------------------------------------------------------------------------------ device entry points
+static int check_arena(shl_ctx* ctx, const void* arena) {
+    if ((reinterpret_cast<uintptr_t>(arena) & 15) != 0)
+        return fail(ctx, SHL_ERR_ARG, "arena base must be 16-byte aligned (and padded by 16 readable bytes)");
+    return SHL_OK;
+}
+
+static int launch_route(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_off, const uint32_t* d_len, uint64_t n,
+                        const shl_parse_out* d_out, const shl_place_out* d_q) {
+    if (!ctx || !d_arena || !d_off || !d_len || !d_out) return fail(ctx, SHL_ERR_ARG, "null pointer");
+    if (int rc = check_arena(ctx, d_arena)) return rc;
+    if (d_q && !ctx->d_ring_values) return fail(ctx, SHL_ERR_NO_RING, "shl_ring_build() has not been called");
+    if (n == 0) return SHL_OK;
+    shl::RouteArgs a{};
+    a.arena = d_arena; a.off = d_off; a.len = d_len; a.n = n; a.out = *d_out;
+    a.code_hist = ctx->d_counters + 2; a.force_scalar = ctx->force_scalar;
+    const uint64_t groups = (n + shl::kGroup - 1) / shl::kGroup;
+    const unsigned blocks = (unsigned)((groups + shl::kWarpsPerBlock - 1) / shl::kWarpsPerBlock);
+    if (d_q) {
+        a.ring_values = ctx->d_ring_values; a.ring_nodes = ctx->d_ring_nodes;
+        a.n_points = ctx->n_points; a.n_hosts = ctx->n_hosts; a.place = *d_q;
+        const size_t sh = (d_q->hist && ctx->n_hosts <= 4096u) ? ctx->n_hosts * 4 : 0;
+        shl::k_route<true><<<blocks, shl::kWarpsPerBlock * 32, sh, ctx->stream>>>(a);
+    } else {
+        shl::k_route<false><<<blocks, shl::kWarpsPerBlock * 32, 0, ctx->stream>>>(a);
+    }
+    ctx->launches++;
+    CU(cudaGetLastError());
+    return SHL_OK;
+}
+
+int shl_parse_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_off, const uint32_t* d_len, uint64_t n,
+                  const shl_parse_out* d_out) {
+    return launch_route(ctx, d_arena, d_off, d_len, n, d_out, nullptr);
+}
+int shl_route_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_off, const uint32_t* d_len, uint64_t n,
+                  const shl_parse_out* d_pout, const shl_place_out* d_qout) {
+    if (!d_qout) return fail(ctx, SHL_ERR_ARG, "shl_route_dev: qout is null");
+    return launch_route(ctx, d_arena, d_off, d_len, n, d_pout, d_qout);
+}
+int shl_frame_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_off, const uint32_t* d_len, uint64_t n,
+                  const uint32_t* d_status, const uint32_t* d_fl, const uint32_t* d_hl, const shl_frame_out* d_out) {
+    if (!ctx || !d_arena || !d_off || !d_len || !d_status || !d_fl || !d_hl || !d_out) return fail(ctx, SHL_ERR_ARG, "null pointer");
+    if (n == 0) return SHL_OK;
+    shl::FrameArgs a{};
+    a.arena = d_arena; a.off = d_off; a.len = d_len; a.n = n; a.status = d_status; a.first_line_len = d_fl; a.headers_len = d_hl;
+    a.out = *d_out;
+    shl::k_frame<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(a);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    return SHL_OK;
+}
+int shl_place_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_key_off, const uint32_t* d_key_len, uint64_t n,
+                  const shl_place_out* d_out) {
+    if (!ctx || !d_arena || !d_key_off || !d_key_len || !d_out) return fail(ctx, SHL_ERR_ARG, "null pointer");
+    if (!ctx->d_ring_values) return fail(ctx, SHL_ERR_NO_RING, "shl_ring_build() has not been called");
+    if (n == 0) return SHL_OK;
+    shl::PlaceArgs a{};
+    a.arena = d_arena; a.key_off = d_key_off; a.key_len = d_key_len; a.n = n;
+    a.ring_values = ctx->d_ring_values; a.ring_nodes = ctx->d_ring_nodes; a.n_points = ctx->n_points; a.n_hosts = ctx->n_hosts;
+    a.out = *d_out;
+    const size_t sh = (d_out->hist && ctx->n_hosts <= 4096u) ? ctx->n_hosts * 4 : 0;
+    shl::k_place<<<(unsigned)((n + 255) / 256), 256, sh, ctx->stream>>>(a);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    return SHL_OK;
+}
+
+// ------------------------------------------------------------------------------------ host-buffer entry points
+static int stage_in(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, const uint64_t* off, const uint32_t* len,
+                    uint64_t n, uint64_t* d_off, uint32_t* d_len) {
+    if (!ctx || !off || !len) return fail(ctx, SHL_ERR_ARG, "null pointer");
+    if (n > ctx->max_msgs || arena_bytes > ctx->max_bytes)
+        return fail(ctx, SHL_ERR_ARG, "batch larger than the capacity given to shl_ctx_create");
+    CU(cudaSetDevice(ctx->device));
+    if (arena)   // NULL: reuse the bytes the previous *_batch call uploaded
+        CU(cudaMemcpyAsync(ctx->d_arena, arena, arena_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(d_off, off, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(d_len, len, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    return SHL_OK;
+}
+#define D2H(dst, src, bytes) do { if (dst) CU(cudaMemcpyAsync((dst), (src), (bytes), cudaMemcpyDeviceToHost, ctx->stream)); } while (0)
+
+static int parse_out_d2h(shl_ctx* ctx, const shl_parse_out* out, uint64_t n) {
+    const shl_parse_out& d = ctx->dp;
+    D2H(out->status, d.status, n * 4); D2H(out->first_line_len, d.first_line_len, n * 4);
+    D2H(out->headers_len, d.headers_len, n * 4); D2H(out->sp1, d.sp1, n * 4); D2H(out->sp2, d.sp2, n * 4);
+    D2H(out->fl_end, d.fl_end, n * 4); D2H(out->slash, d.slash, n * 4); D2H(out->status_code, d.status_code, n * 4);
+    D2H(out->n_headers, d.n_headers, n * 4); D2H(out->hdr_base, d.hdr_base, n * 4); D2H(out->content_len, d.content_len, n * 8);
+    if (out->hdr || out->hdr_used) {
+        // the record count is only known after the kernel: fetch it, then copy exactly that many
+        CU(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, 8, cudaMemcpyDeviceToHost, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+        const uint64_t used = ctx->h_counters[0];
+        if (out->hdr_used) *out->hdr_used = used;
+        const uint64_t copy = std::min<uint64_t>(std::min<uint64_t>(used, d.hdr_cap), out->hdr_cap);
+        if (out->hdr && copy) CU(cudaMemcpyAsync(out->hdr, d.hdr, copy * sizeof(shl_hdr_span), cudaMemcpyDeviceToHost, ctx->stream));
+        if (used > d.hdr_cap || (out->hdr && used > out->hdr_cap))
+            return fail(ctx, SHL_ERR_CAPACITY, "header record arena overflowed: raise max_records / hdr_cap");
+    }
+    return SHL_OK;
+}
+static int place_out_d2h(shl_ctx* ctx, const shl_place_out* out, uint64_t n) {
+    const shl_place_out& d = ctx->dq;
+    D2H(out->md5, d.md5, n * 16); D2H(out->hash, d.hash, n * 4); D2H(out->node, d.node, n * 4);
+    if (out->hist) {
+        // `hist` is ADDED to: bring the device bins back through the pinned mirror
+        std::vector<uint64_t> tmp(ctx->n_hosts);
+        CU(cudaMemcpyAsync(tmp.data(), ctx->d_hist, (size_t)ctx->n_hosts * 8, cudaMemcpyDeviceToHost, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+        for (uint32_t i = 0; i < ctx->n_hosts; i++) out->hist[i] += tmp[i];
+    }
+    return SHL_OK;
+}
+
+int shl_parse_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, const uint64_t* off, const uint32_t* len,
+                    uint64_t n, const shl_parse_out* out) {
+    if (!out) return fail(ctx, SHL_ERR_ARG, "out is null");
+    if (int rc = stage_in(ctx, arena, arena_bytes, off, len, n, ctx->d_off, ctx->d_len)) return rc;
+    CU(cudaMemsetAsync(ctx->d_counters, 0, 8, ctx->stream));
+    if (int rc = shl_parse_dev(ctx, ctx->d_arena, ctx->d_off, ctx->d_len, n, &ctx->dp)) return rc;
+    return parse_out_d2h(ctx, out, n);
+}
+
+int shl_route_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, const uint64_t* off, const uint32_t* len,
+                    uint64_t n, const shl_parse_out* pout, const shl_place_out* qout) {
+    if (!pout || !qout) return fail(ctx, SHL_ERR_ARG, "out is null");
+    if (ctx && !ctx->d_ring_values) return fail(ctx, SHL_ERR_NO_RING, "shl_ring_build() has not been called");
+    if (int rc = stage_in(ctx, arena, arena_bytes, off, len, n, ctx->d_off, ctx->d_len)) return rc;
+    CU(cudaMemsetAsync(ctx->d_counters, 0, 8, ctx->stream));
+    shl_place_out dq = ctx->dq;
+    dq.hist = qout->hist ? ctx->d_hist : nullptr;
+    if (dq.hist) CU(cudaMemsetAsync(ctx->d_hist, 0, (size_t)ctx->n_hosts * 8, ctx->stream));
+    if (int rc = shl_route_dev(ctx, ctx->d_arena, ctx->d_off, ctx->d_len, n, &ctx->dp, &dq)) return rc;
+    if (int rc = parse_out_d2h(ctx, pout, n)) return rc;
+    return place_out_d2h(ctx, qout, n);
+}
+
+int shl_place_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, const uint64_t* key_off, const uint32_t* key_len,
+                    uint64_t n, const shl_place_out* out) {
+    if (!out) return fail(ctx, SHL_ERR_ARG, "out is null");
+    if (ctx && !ctx->d_ring_values) return fail(ctx, SHL_ERR_NO_RING, "shl_ring_build() has not been called");
+    if (int rc = stage_in(ctx, arena, arena_bytes, key_off, key_len, n, ctx->d_koff, ctx->d_klen)) return rc;
+    shl_place_out dq = ctx->dq;
+    dq.hist = out->hist ? ctx->d_hist : nullptr;
+    if (dq.hist) CU(cudaMemsetAsync(ctx->d_hist, 0, (size_t)ctx->n_hosts * 8, ctx->stream));
+    if (int rc = shl_place_dev(ctx, ctx->d_arena, ctx->d_koff, ctx->d_klen, n, &dq)) return rc;
+    return place_out_d2h(ctx, out, n);
+}
+
+int shl_frame_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, const uint64_t* off, const uint32_t* len,
+                    uint64_t n, const uint32_t* status, const uint32_t* first_line_len, const uint32_t* headers_len,
+                    const shl_frame_out* out) {
+    if (!out || !status || !first_line_len || !headers_len) return fail(ctx, SHL_ERR_ARG, "null pointer");
+    if (int rc = stage_in(ctx, arena, arena_bytes, off, len, n, ctx->d_off, ctx->d_len)) return rc;
+    // the parse fields travel with the call so it can be used on its own (they are tiny next to the arena)
+    CU(cudaMemcpyAsync(ctx->dp.status, status, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->dp.first_line_len, first_line_len, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->dp.headers_len, headers_len, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemsetAsync(ctx->d_counters + 1, 0, 8, ctx->stream));
+    if (int rc = shl_frame_dev(ctx, ctx->d_arena, ctx->d_off, ctx->d_len, n, ctx->dp.status, ctx->dp.first_line_len,
+                               ctx->dp.headers_len, &ctx->df)) return rc;
+    const shl_frame_out& d = ctx->df;
+    D2H(out->fstatus, d.fstatus, n * 4); D2H(out->n_chunks, d.n_chunks, n * 4); D2H(out->chunk_base, d.chunk_base, n * 4);
+    D2H(out->body_end, d.body_end, n * 8); D2H(out->body_bytes, d.body_bytes, n * 8); D2H(out->last_call, d.last_call, n * 4);
+    if (out->chunk || out->chunk_used) {
+        CU(cudaMemcpyAsync(ctx->h_counters + 1, ctx->d_counters + 1, 8, cudaMemcpyDeviceToHost, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+        const uint64_t used = ctx->h_counters[1];
+        if (out->chunk_used) *out->chunk_used = used;
+        const uint64_t copy = std::min<uint64_t>(std::min<uint64_t>(used, d.chunk_cap), out->chunk_cap);
+        if (out->chunk && copy) CU(cudaMemcpyAsync(out->chunk, d.chunk, copy * sizeof(shl_chunk_span), cudaMemcpyDeviceToHost, ctx->stream));
+        if (used > d.chunk_cap || (out->chunk && used > out->chunk_cap))
+            return fail(ctx, SHL_ERR_CAPACITY, "chunk record arena overflowed: raise max_records / chunk_cap");
+    }
+    return SHL_OK;
+}
+
+int shl_chunk_header_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, const uint64_t* off, const uint32_t* len,
+                           uint64_t n, int32_t* hdr_len, uint64_t* size, uint8_t* ok) {
+    if (!hdr_len || !size || !ok) return fail(ctx, SHL_ERR_ARG, "null pointer");
+    if (int rc = stage_in(ctx, arena, arena_bytes, off, len, n, ctx->d_off, ctx->d_len)) return rc;
+    if (n) {
+        shl::k_chunk_header<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(ctx->d_arena, ctx->d_off, ctx->d_len, n,
+                                                                                 ctx->d_ch_len, ctx->d_ch_size, ctx->d_ch_ok);
+        ctx->launches++;
+        CU(cudaGetLastError());
+    }
+    D2H(hdr_len, ctx->d_ch_len, n * 4); D2H(size, ctx->d_ch_size, n * 8); D2H(ok, ctx->d_ch_ok, n);
+    return SHL_OK;
+}
+
+int shl_code_hist(shl_ctx* ctx, uint64_t* out64, int reset) {
+    if (!ctx || !out64) return SHL_ERR_ARG;
+    CU(cudaMemcpyAsync(ctx->h_counters + 2, ctx->d_counters + 2, 64 * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (reset) CU(cudaMemsetAsync(ctx->d_counters + 2, 0, 64 * 8, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    memcpy(out64, ctx->h_counters + 2, 64 * 8);
+    return SHL_OK;
+}
+void* shl_code_hist_dev(shl_ctx* ctx) { return ctx ? (void*)(ctx->d_counters + 2) : nullptr; }
+void* shl_node_hist_dev(shl_ctx* ctx) { return ctx ? (void*)ctx->d_hist : nullptr; }
+int shl_set_force_scalar(shl_ctx* ctx, int on) { if (!ctx) return SHL_ERR_ARG; ctx->force_scalar = on ? 1 : 0; return SHL_OK; }
+
+// ------------------------------------------------------------------------------------ corpora
+int shl_corpus_lengths_host(uint64_t seed, uint64_t first, uint64_t n, int kind, uint32_t* len) {
+    if (!len) return SHL_ERR_ARG;
+    for (uint64_t i = 0; i < n; i++) len[i] = shl::gen_message(seed, first + i, kind, nullptr);
+    return SHL_OK;
+}
+int shl_corpus_fill_host(uint64_t seed, uint64_t first, uint64_t n, int kind, const uint64_t* off, uint8_t* arena) {
+    if (!off || !arena) return SHL_ERR_ARG;
+    for (uint64_t i = 0; i < n; i++) shl::gen_message(seed, first + i, kind, arena + off[i]);
+    return SHL_OK;
+}
+}  // extern "C"
+
+namespace shl {
+__global__ void k_corpus_lengths(uint64_t seed, uint64_t first, uint64_t n, int kind, uint32_t* len) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) len[i] = gen_message(seed, first + i, kind, nullptr);
+}
+__global__ void k_corpus_fill(uint64_t seed, uint64_t first, uint64_t n, int kind, const uint64_t* off, uint8_t* arena) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) gen_message(seed, first + i, kind, arena + off[i]);
+}
+}  // namespace shl
+
+extern "C" {
+int shl_corpus_lengths_dev(shl_ctx* ctx, uint64_t seed, uint64_t first, uint64_t n, int kind, uint32_t* d_len) {
+    if (!ctx || !d_len) return SHL_ERR_ARG;
+    if (n) { shl::k_corpus_lengths<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(seed, first, n, kind, d_len); ctx->launches++; }
+    CU(cudaGetLastError());
+    return SHL_OK;
+}
+int shl_corpus_fill_dev(shl_ctx* ctx, uint64_t seed, uint64_t first, uint64_t n, int kind, const uint64_t* d_off, uint8_t* d_arena) {
+    if (!ctx || !d_off || !d_arena) return SHL_ERR_ARG;
+    if (n) { shl::k_corpus_fill<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(seed, first, n, kind, d_off, d_arena); ctx->launches++; }
+    CU(cudaGetLastError());
+    return SHL_OK;
+}
+}  // extern "C"

@@ -1,0 +1,167 @@
+// frame_kernel.cuh — K2: chunked-body framing, and the single-header primitive.
+//
+// Replaces HttpParser._parse_chunked / _parse_chunk_size and CHUNK_HEADER_RX
+// (/root/reference/src/python/shellac/server/HttpParser.py:39-40, 234-301) for a whole message
+// (buf_len == 0 at every chunk header, so the stale-buf_len quirk of :296 cannot arise here).
+// The walk is a pointer chase (each header says where the next one is), so it is latency-bound,
+// not bandwidth-bound: bodies are skipped by arithmetic and never read.  One thread per message,
+// two walks: count, allocate the message's chunk records with one atomic, emit.
+#pragma once
+#include "shl_device.cuh"
+
+namespace shl {
+
+// CHUNK_HEADER_RX = (\r\n)?[a-z0-9]+(;[a-z0-9]+="?[a-z0-9\-_]+"?)?\r\n , IGNORECASE, anchored.
+// Returns the match length at m[p:L) or -1; [a,b) is the size run.
+__device__ __forceinline__ int64_t chunk_header_match(const uint8_t* m, int64_t p, int64_t L, int64_t& a, int64_t& b) {
+    int64_t i = p;
+    if (i + 1 < L && ldb(m + i) == '\r' && ldb(m + i + 1) == '\n') i += 2;
+    a = i;
+    while (i < L && is_alnum(ldb(m + i))) i++;
+    if (i == a) return -1;
+    b = i;
+    if (i + 1 < L && ldb(m + i) == '\r' && ldb(m + i + 1) == '\n') return i + 2 - p;
+    if (i < L && ldb(m + i) == ';') {
+        int64_t j = i + 1, k = j;
+        while (j < L && is_alnum(ldb(m + j))) j++;
+        if (j == k || j >= L || ldb(m + j) != '=') return -1;
+        j++;
+        if (j < L && ldb(m + j) == '"') j++;
+        k = j;
+        while (j < L) { const uint32_t c = ldb(m + j); if (!(is_alnum(c) || c == '-' || c == '_')) break; j++; }
+        if (j == k) return -1;
+        if (j < L && ldb(m + j) == '"') j++;
+        if (j + 1 < L && ldb(m + j) == '\r' && ldb(m + j + 1) == '\n') return j + 2 - p;
+    }
+    return -1;
+}
+
+// int(size, 16) (HttpParser.py:234-241): optional 0x/0X then hex digits; false = ValueError.
+// Saturates at 2^63: such a chunk can never be satisfied by a < 2 GiB message.
+__device__ __forceinline__ bool py_int16(const uint8_t* s, int64_t n, unsigned long long& v) {
+    int64_t i = 0;
+    if (n >= 2 && ldb(s) == '0' && (ldb(s + 1) | 32u) == 'x') i = 2;
+    if (i == n) return false;
+    unsigned long long acc = 0;
+    for (; i < n; i++) {
+        const int h = hexval(ldb(s + i));
+        if (h < 0) return false;
+        if (acc >> 59) acc = 1ull << 63; else acc = acc * 16ull + (unsigned long long)h;
+        if (acc > (1ull << 63)) acc = 1ull << 63;
+    }
+    v = acc;
+    return true;
+}
+
+struct FrameArgs {
+    const uint8_t* arena; const uint64_t* off; const uint32_t* len; uint64_t n;
+    const uint32_t* status; const uint32_t* first_line_len; const uint32_t* headers_len;
+    shl_frame_out out;
+};
+
+struct Walk { uint32_t fs, nch, last; int64_t end; unsigned long long bytes; };
+
+template <bool kEmit>
+__device__ __forceinline__ Walk walk_chunks(const uint8_t* m, int64_t L, int64_t p, shl_chunk_span* dst, uint32_t cap) {
+    Walk w; w.fs = SHL_S_INCOMPLETE_BODY; w.nch = 0; w.last = 0; w.bytes = 0;
+    while (p < L) {
+        int64_t a, b;
+        const int64_t idx = chunk_header_match(m, p, L, a, b);
+        if (idx < 0) { w.last = (uint32_t)(L - p); p = L; break; }                 // :255-256
+        unsigned long long size;
+        if (!py_int16(m + a, b - a, size)) { w.fs = SHL_E_CHUNK_HEX; break; }       // :239-241
+        const int64_t left = L - (p + idx);
+        if (size == 0ull) {                                                          // :268-287
+            if (left >= 2 && ldb(m + p + idx) == '\r' && ldb(m + p + idx + 1) == '\n') {
+                w.last = (uint32_t)(idx + 2); p += idx + 2; w.fs = SHL_S_OK;
+            } else {
+                p += idx; w.last = (uint32_t)idx;
+                if (p < L) { w.last = (uint32_t)(L - p); p = L; }
+            }
+            break;
+        }
+        if ((unsigned long long)left < size) { w.last = (uint32_t)(idx + left); p = L; break; }   // :291-294
+        if (kEmit && w.nch < cap) {
+            shl_chunk_span c;
+            c.hdr_off = (uint32_t)p; c.hdr_len = (uint32_t)idx; c.data_off = (uint32_t)(p + idx); c.data_len = (uint32_t)size;
+            dst[w.nch] = c;
+        }
+        w.nch++;
+        w.bytes += size; w.last = (uint32_t)(idx + (int64_t)size);
+        p += idx + (int64_t)size;                                                    // :295-301
+    }
+    w.end = p;
+    return w;
+}
+
+__global__ void __launch_bounds__(128) k_frame(const FrameArgs a) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.n) return;
+    const uint32_t st = a.status[i];
+    uint32_t fs = 0xffu, nch = 0, last = 0, base = 0; uint64_t end = 0, bytes = 0;
+    if ((st & SHL_F_CHUNKED) && (st & SHL_F_HEADERS_COMPLETE) && !(st & SHL_F_MESSAGE_COMPLETE) && (st & 0xffu) < 16u) {
+        const uint8_t* m = a.arena + a.off[i];
+        const int64_t L = a.len[i], p0 = (int64_t)a.first_line_len[i] + a.headers_len[i];
+        Walk w = walk_chunks<false>(m, L, p0, nullptr, 0);
+        fs = w.fs; nch = w.nch; last = w.last; end = (uint64_t)w.end; bytes = w.bytes;
+        if (nch) {
+            const unsigned long long b = atomicAdd(reinterpret_cast<unsigned long long*>(a.out.chunk_used), (unsigned long long)nch);
+            base = (uint32_t)b;
+            if (b + nch <= a.out.chunk_cap) walk_chunks<true>(m, L, p0, a.out.chunk + b, nch);
+            else { fs = SHL_E_LIB_RECORDS_FULL; nch = 0; }
+        }
+    }
+    a.out.fstatus[i] = fs; a.out.n_chunks[i] = nch; a.out.chunk_base[i] = base;
+    a.out.body_end[i] = end; a.out.body_bytes[i] = bytes; a.out.last_call[i] = last;
+}
+
+// One CHUNK_HEADER_RX.match + _parse_chunk_size at the start of each window (HttpParser.py:253-261),
+// the primitive the incremental facade needs.
+__global__ void __launch_bounds__(128) k_chunk_header(const uint8_t* arena, const uint64_t* off, const uint32_t* len,
+                                                      uint64_t n, int32_t* hdr_len, uint64_t* size, uint8_t* ok) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int64_t a = 0, b = 0;
+    const uint8_t* m = arena + off[i];
+    const int64_t idx = chunk_header_match(m, 0, (int64_t)len[i], a, b);
+    unsigned long long v = 0; bool good = false;
+    if (idx >= 0) good = py_int16(m + a, b - a, v);
+    hdr_len[i] = (int32_t)idx; size[i] = good ? v : 0ull; ok[i] = good ? 1 : 0;
+}
+
+// ----------------------------------------------------------------------------------- K3+K4
+// key -> MD5 -> LE32 -> continuum lower-bound -> node (+ per-node histogram), one key per thread.
+struct PlaceArgs {
+    const uint8_t* arena; const uint64_t* key_off; const uint32_t* key_len; uint64_t n;
+    const uint32_t* ring_values; const uint32_t* ring_nodes; uint32_t n_points, n_hosts;
+    shl_place_out out;
+};
+
+__global__ void __launch_bounds__(256) k_place(const PlaceArgs a) {
+    extern __shared__ uint32_t s_hist[];
+    const bool smem_hist = a.out.hist != nullptr && a.n_hosts <= 4096u;
+    if (smem_hist) for (uint32_t i = threadIdx.x; i < a.n_hosts; i += blockDim.x) s_hist[i] = 0u;
+    __syncthreads();
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < a.n) {
+        uint32_t h[4];
+        md5_key(a.arena + a.key_off[i], a.key_len[i], h);
+        const uint32_t node = ring_lookup(a.ring_values, a.ring_nodes, a.n_points, a.n_hosts, h[0]);
+        if (a.out.md5) {
+            uint32_t* d = reinterpret_cast<uint32_t*>(a.out.md5) + 4 * i;
+            d[0] = h[0]; d[1] = h[1]; d[2] = h[2]; d[3] = h[3];
+        }
+        if (a.out.hash) a.out.hash[i] = h[0];
+        if (a.out.node) a.out.node[i] = node;
+        if (a.out.hist) {
+            if (smem_hist) atomicAdd(&s_hist[node], 1u);
+            else atomicAdd(reinterpret_cast<unsigned long long*>(a.out.hist) + node, 1ull);
+        }
+    }
+    __syncthreads();
+    if (smem_hist)
+        for (uint32_t i = threadIdx.x; i < a.n_hosts; i += blockDim.x)
+            if (s_hist[i]) atomicAdd(reinterpret_cast<unsigned long long*>(a.out.hist) + i, (unsigned long long)s_hist[i]);
+}
+
+}  // namespace shl

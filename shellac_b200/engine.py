@@ -1,0 +1,194 @@
+"""Engine: the Python owner of one shl_ctx (one GPU), the object a Shellac server would hold where
+it holds `self._mc = pylibmc.Client([...], binary=True, behaviors={'ketama': True})` today
+(Server.py:81-83).  It packs batches into pinned arenas and calls the C ABI through ctypes.
+
+No CPU fallback: constructing an Engine without the built library or without a CUDA device raises.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _native as N
+from .batch import Arena, FrameOut, ParseOut, PlaceOut
+
+
+def _check(lib, ctx, rc, what):
+    if rc != 0:
+        msg = lib.shl_last_error(ctx)
+        raise N.ShellacError('%s failed (%d): %s' % (what, rc, msg.decode() if msg else '?'))
+
+
+class Engine(object):
+    def __init__(self, device=0, max_msgs=1 << 16, max_bytes=1 << 26, max_records=0):
+        self.lib = N.lib()
+        if self.lib.shl_device_count() <= 0:
+            raise N.ShellacError('no CUDA device: shellac_b200 has no CPU fallback')
+        h = C.c_void_p()
+        rc = self.lib.shl_ctx_create(device, max_msgs, max_bytes, max_records, C.byref(h))
+        _check(self.lib, None, rc, 'shl_ctx_create')
+        self.ctx = h
+        self.device, self.max_msgs, self.max_bytes = device, max_msgs, max_bytes
+        self.max_records = max_records if max_records else max(max_bytes // 16, 1024)
+        self._pinned = []
+        self.n_hosts = 0
+
+    # -- memory -----------------------------------------------------------------------------
+    def pinned(self, n, dtype):
+        """A page-locked numpy array (zero-filled) that lives as long as the engine."""
+        dt = np.dtype(dtype)
+        nbytes = max(int(n), 1) * dt.itemsize
+        p = C.c_void_p()
+        _check(self.lib, self.ctx, self.lib.shl_pinned_alloc(C.byref(p), nbytes), 'shl_pinned_alloc')
+        self._pinned.append(p)
+        buf = (C.c_uint8 * nbytes).from_address(p.value)
+        a = np.frombuffer(buf, dtype=np.uint8)
+        a[:] = 0
+        return a.view(dt)
+
+    def pack(self, messages, align=1):
+        return Arena.pack(messages, alloc=self.pinned, align=align)
+
+    def dev_alloc(self, nbytes):
+        p = C.c_void_p()
+        _check(self.lib, self.ctx, self.lib.shl_device_alloc(self.ctx, C.byref(p), int(nbytes)), 'shl_device_alloc')
+        return p.value
+
+    def dev_free(self, dptr):
+        _check(self.lib, self.ctx, self.lib.shl_device_free(self.ctx, dptr), 'shl_device_free')
+
+    def h2d(self, dptr, arr, nbytes=None):
+        n = arr.nbytes if nbytes is None else int(nbytes)
+        _check(self.lib, self.ctx, self.lib.shl_memcpy_h2d(self.ctx, dptr, arr.ctypes.data, n), 'shl_memcpy_h2d')
+
+    def d2h(self, arr, dptr, nbytes=None):
+        n = arr.nbytes if nbytes is None else int(nbytes)
+        _check(self.lib, self.ctx, self.lib.shl_memcpy_d2h(self.ctx, arr.ctypes.data, dptr, n), 'shl_memcpy_d2h')
+
+    def memset(self, dptr, value, nbytes):
+        _check(self.lib, self.ctx, self.lib.shl_memset_dev(self.ctx, dptr, value, int(nbytes)), 'shl_memset_dev')
+
+    def sync(self):
+        _check(self.lib, self.ctx, self.lib.shl_sync(self.ctx), 'shl_sync')
+
+    def event(self, slot):
+        _check(self.lib, self.ctx, self.lib.shl_event_record(self.ctx, slot), 'shl_event_record')
+
+    def elapsed_ms(self, a, b):
+        ms = C.c_float()
+        _check(self.lib, self.ctx, self.lib.shl_event_elapsed_ms(self.ctx, a, b, C.byref(ms)), 'shl_event_elapsed_ms')
+        return float(ms.value)
+
+    def launches(self):
+        return int(self.lib.shl_launch_count(self.ctx))
+
+    def set_force_scalar(self, on):
+        _check(self.lib, self.ctx, self.lib.shl_set_force_scalar(self.ctx, 1 if on else 0), 'shl_set_force_scalar')
+
+    # -- ring (pylibmc.Client(servers, behaviors={'ketama': True}), Server.py:81-83) ----------
+    def ring_build(self, hosts, ports=None, weights=None, mode=N.RING_KETAMA):
+        n = len(hosts)
+        arr = (C.c_char_p * n)(*[h.encode() if isinstance(h, str) else h for h in hosts])
+        p = np.asarray(ports if ports is not None else [11211] * n, dtype=np.uint32)
+        w = np.asarray(weights, dtype=np.uint32) if weights is not None else None
+        rc = self.lib.shl_ring_build(self.ctx, arr, p.ctypes.data, w.ctypes.data if w is not None else None, n, mode)
+        _check(self.lib, self.ctx, rc, 'shl_ring_build')
+        self.n_hosts = n
+
+    def ring_export(self):
+        npts, nh = C.c_uint32(), C.c_uint32()
+        _check(self.lib, self.ctx, self.lib.shl_ring_size(self.ctx, C.byref(npts), C.byref(nh)), 'shl_ring_size')
+        v, nd = np.zeros(max(npts.value, 1), np.uint32), np.zeros(max(npts.value, 1), np.uint32)
+        _check(self.lib, self.ctx, self.lib.shl_ring_export(self.ctx, v.ctypes.data, nd.ctypes.data, npts.value), 'shl_ring_export')
+        return v[:npts.value], nd[:npts.value]
+
+    # -- host-buffer entry points ------------------------------------------------------------
+    def _hdr_cap(self, arena, cap):
+        return int(cap) if cap else min(self.max_records, max(64, arena.nbytes // 4 + 64))
+
+    def parse(self, arena, hdr_cap=0, sync=True, out=None):
+        out = out or ParseOut(arena.n, self._hdr_cap(arena, hdr_cap), alloc=self.pinned)
+        s = out.struct()
+        rc = self.lib.shl_parse_batch(self.ctx, arena.data.ctypes.data, arena.nbytes, arena.off.ctypes.data,
+                                      arena.len.ctypes.data, arena.n, C.byref(s))
+        _check(self.lib, self.ctx, rc, 'shl_parse_batch')
+        if sync:
+            self.sync()
+        return out
+
+    def frame(self, arena, pout, chunk_cap=0, reuse_arena=False, sync=True, out=None):
+        cap = int(chunk_cap) if chunk_cap else min(self.max_records, max(64, arena.nbytes // 8 + 64))
+        out = out or FrameOut(arena.n, cap, alloc=self.pinned)
+        s = out.struct()
+        rc = self.lib.shl_frame_batch(self.ctx, None if reuse_arena else arena.data.ctypes.data, arena.nbytes,
+                                      arena.off.ctypes.data, arena.len.ctypes.data, arena.n,
+                                      pout.status.ctypes.data, pout.first_line_len.ctypes.data,
+                                      pout.headers_len.ctypes.data, C.byref(s))
+        _check(self.lib, self.ctx, rc, 'shl_frame_batch')
+        if sync:
+            self.sync()
+        return out
+
+    def route(self, arena, hdr_cap=0, sync=True, pout=None, qout=None):
+        pout = pout or ParseOut(arena.n, self._hdr_cap(arena, hdr_cap), alloc=self.pinned)
+        qout = qout or PlaceOut(arena.n, self.n_hosts, alloc=self.pinned)
+        ps, qs = pout.struct(), qout.struct()
+        rc = self.lib.shl_route_batch(self.ctx, arena.data.ctypes.data, arena.nbytes, arena.off.ctypes.data,
+                                      arena.len.ctypes.data, arena.n, C.byref(ps), C.byref(qs))
+        _check(self.lib, self.ctx, rc, 'shl_route_batch')
+        if sync:
+            self.sync()
+        return pout, qout
+
+    def place(self, arena, key_off=None, key_len=None, sync=True, out=None):
+        key_off = arena.off if key_off is None else key_off
+        key_len = arena.len if key_len is None else key_len
+        n = len(key_off)
+        out = out or PlaceOut(n, self.n_hosts, alloc=self.pinned)
+        s = out.struct()
+        rc = self.lib.shl_place_batch(self.ctx, arena.data.ctypes.data, arena.nbytes, key_off.ctypes.data,
+                                      key_len.ctypes.data, n, C.byref(s))
+        _check(self.lib, self.ctx, rc, 'shl_place_batch')
+        if sync:
+            self.sync()
+        return out
+
+    def chunk_header(self, arena):
+        n = arena.n
+        hl, sz, ok = self.pinned(n, np.int32), self.pinned(n, np.uint64), self.pinned(n, np.uint8)
+        rc = self.lib.shl_chunk_header_batch(self.ctx, arena.data.ctypes.data, arena.nbytes, arena.off.ctypes.data,
+                                             arena.len.ctypes.data, n, hl.ctypes.data, sz.ctypes.data, ok.ctypes.data)
+        _check(self.lib, self.ctx, rc, 'shl_chunk_header_batch')
+        self.sync()
+        return hl[:n], sz[:n], ok[:n]
+
+    def code_hist(self, reset=True):
+        out = np.zeros(N.N_CODES, np.uint64)
+        _check(self.lib, self.ctx, self.lib.shl_code_hist(self.ctx, out.ctypes.data, 1 if reset else 0), 'shl_code_hist')
+        return out
+
+    # -- synthetic corpora (BASELINE.json configs 2/4/5) --------------------------------------
+    def corpus_host(self, seed, first, n, kind=0):
+        """Generate messages [first, first+n) on the HOST into a pinned arena."""
+        ln = self.pinned(n, np.uint32)
+        _check(self.lib, self.ctx, self.lib.shl_corpus_lengths_host(seed, first, n, kind, ln.ctypes.data), 'corpus_lengths')
+        off = self.pinned(n, np.uint64)
+        if n > 1:
+            np.cumsum(ln[:n - 1], dtype=np.uint64, out=off[1:n])
+        total = int(off[n - 1] + ln[n - 1]) if n else 0
+        data = self.pinned(total + 64, np.uint8)
+        _check(self.lib, self.ctx, self.lib.shl_corpus_fill_host(seed, first, n, kind, off.ctypes.data, data.ctypes.data), 'corpus_fill')
+        return Arena(data, off[:n], ln[:n])
+
+    def close(self):
+        if getattr(self, 'ctx', None):
+            self.lib.shl_ctx_destroy(self.ctx)
+            self.ctx = None
+            for p in self._pinned:
+                self.lib.shl_pinned_free(p)
+            self._pinned = []
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:   # noqa: BLE001 - interpreter shutdown
+            pass

@@ -1,0 +1,356 @@
+"""GPU parity tests proper (-m gpu): every call goes through the C ABI (ctypes ->
+libshellac_b200.so -> sm_100a kernels) and is compared with (a) the golden vectors the unmodified
+reference produced and (b) the CPU oracle on the same seeded inputs.  Bar: bit-exact."""
+import hashlib
+
+import numpy as np
+import pytest
+
+from shellac_b200 import _native as N
+from shellac_b200.batch import Arena, MessageView
+from tests import oracle_lib as O
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope='module')
+def eng():
+    from shellac_b200 import build as B
+    from shellac_b200.engine import Engine
+    B.build()
+    e = Engine(device=0, max_msgs=1 << 20, max_bytes=(1 << 30) + (1 << 28), max_records=1 << 25)
+    yield e
+    e.close()
+
+
+# ------------------------------------------------------------------------------- helpers
+def _records(out, n):
+    """Header records of messages [0,n) in message order, as one uint64 array (+ per-msg counts)."""
+    cnt = out.n_headers[:n].astype(np.int64)
+    base = out.hdr_base[:n].astype(np.int64)
+    total = int(cnt.sum())
+    if total == 0:
+        return np.zeros(0, np.uint64)
+    excl = np.cumsum(cnt) - cnt
+    idx = np.repeat(base - excl, cnt) + np.arange(total)
+    return out.hdr.view(np.uint64)[idx]
+
+
+def _describe(ar, i, g, o):
+    m = ar.message(i)
+    fields = [f for f, _ in N.PARSE_FIELDS if f != 'hdr_base']
+    return {'i': i, 'msg': m[:160], 'len': len(m),
+            'gpu': {f: int(getattr(g, f)[i]) for f in fields}, 'orc': {f: int(getattr(o, f)[i]) for f in fields},
+            'gpu_code': N.CODE_NAMES.get(int(g.status[i]) & 0xff), 'orc_code': N.CODE_NAMES.get(int(o.status[i]) & 0xff)}
+
+
+def assert_parse_equal(ar, g, o, what):
+    n = ar.n
+    bad = np.zeros(n, bool)
+    for f, _ in N.PARSE_FIELDS:
+        if f == 'hdr_base':
+            continue
+        bad |= getattr(g, f)[:n] != getattr(o, f)[:n]
+    if bad.any():
+        w = np.flatnonzero(bad)
+        raise AssertionError('%s: %d/%d messages differ; first: %r' % (what, len(w), n, [_describe(ar, int(i), g, o) for i in w[:4]]))
+    rg, ro = _records(g, n), _records(o, n)
+    if len(rg) != len(ro) or (rg != ro).any():
+        cnt = o.n_headers[:n].astype(np.int64)
+        owner = np.repeat(np.arange(n), cnt)
+        k = int(np.flatnonzero(rg != ro)[0])
+        i = int(owner[k])
+        b_g, b_o, c = int(g.hdr_base[i]), int(o.hdr_base[i]), int(cnt[i])
+        raise AssertionError('%s: header records differ, first at message %d: %r\n gpu=%r\n orc=%r' % (
+            what, i, ar.message(i)[:300], g.hdr[b_g:b_g + c].tolist(), o.hdr[b_o:b_o + c].tolist()))
+    assert int(g.hdr_used[0]) == int(o.hdr_used[0]), what
+
+
+def assert_frame_equal(ar, g, o, what):
+    n = ar.n
+    for f, _ in N.FRAME_FIELDS:
+        if f == 'chunk_base':
+            continue
+        a, b = getattr(g, f)[:n], getattr(o, f)[:n]
+        if (a != b).any():
+            i = int(np.flatnonzero(a != b)[0])
+            raise AssertionError('%s: frame field %s differs at %d: gpu=%d orc=%d msg=%r' % (
+                what, f, i, int(a[i]), int(b[i]), ar.message(i)[:300]))
+    for i in np.flatnonzero(o.n_chunks[:n]):
+        c = int(o.n_chunks[i])
+        x = g.chunk[int(g.chunk_base[i]):int(g.chunk_base[i]) + c]
+        y = o.chunk[int(o.chunk_base[i]):int(o.chunk_base[i]) + c]
+        assert (x == y).all(), (what, int(i), x.tolist(), y.tolist())
+
+
+def scatter_pack(eng, msgs, rng):
+    """Pack with random 0..15-byte gaps so message starts hit every 16-byte alignment, and fill
+    the gaps with bytes that would confuse a parser reading outside [off, off+len)."""
+    msgs = [m.encode('latin-1') if isinstance(m, str) else m for m in msgs]
+    gaps = rng.integers(0, 16, len(msgs))
+    junk = b'\r\n\r\n: \r\n \r\n\r\n: '
+    parts, off, pos = [], [], 0
+    for m, gp in zip(msgs, gaps):
+        parts.append(junk[:gp]); pos += gp
+        off.append(pos); parts.append(m); pos += len(m)
+    blob = b''.join(parts) + junk
+    data = eng.pinned(len(blob) + 64, np.uint8)
+    data[:len(blob)] = np.frombuffer(blob, np.uint8)
+    a_off, a_len = eng.pinned(len(msgs), np.uint64), eng.pinned(len(msgs), np.uint32)
+    a_off[:] = off
+    a_len[:] = [len(m) for m in msgs]
+    return Arena(data, a_off, a_len)
+
+
+# ------------------------------------------------------------------------------- golden
+@pytest.mark.parametrize('force_scalar', [False, True])
+def test_golden_whole_messages(eng, golden, force_scalar):
+    """Config 1: the reference's own corpus (test/HttpParserTests.py literals + seeded poison)."""
+    eng.set_force_scalar(force_scalar)
+    try:
+        ar = eng.pack([w['msg'] for w in golden['whole']])
+        po = eng.parse(ar)
+        fo = eng.frame(ar, po, reuse_arena=True)
+    finally:
+        eng.set_force_scalar(False)
+    bad = []
+    for i, w in enumerate(golden['whole']):
+        v = MessageView(ar.message(i), po, i, fo, text=True)
+        d = O.diff_observation(v, w['obs'])
+        if d:
+            bad.append((w['id'], w['msg'][:100], d))
+    assert not bad, (len(bad), bad[:5])
+
+
+def test_golden_vs_oracle_soa_all_alignments(eng, golden):
+    rng = np.random.default_rng(1)
+    msgs = [w['msg'] for w in golden['whole']]
+    for rep in range(3):
+        ar = scatter_pack(eng, msgs, rng)
+        g = eng.parse(ar)
+        o = O.orc_parse(ar)
+        assert_parse_equal(ar, g, o, 'golden scatter %d' % rep)
+        assert_frame_equal(ar, eng.frame(ar, g, reuse_arena=True), O.orc_frame(ar, o), 'golden frame %d' % rep)
+
+
+def test_golden_streams_and_gzip(eng, golden):
+    for s in golden['streams']:
+        data, start = s['stream'], 0
+        for exp in s['msgs']:
+            ar = eng.pack([data[start:]])
+            po = eng.parse(ar)
+            v = MessageView(ar.message(0), po, 0, eng.frame(ar, po, reuse_arena=True), text=True)
+            assert not O.diff_observation(v, {k: exp[k] for k in exp if k != 'start'})
+            start += v.consumed()
+        assert start == len(data)
+    for name, z in golden['gzip'].items():
+        ar = eng.pack([z['msg']])
+        po = eng.parse(ar)
+        v = MessageView(ar.message(0), po, 0, eng.frame(ar, po, reuse_arena=True), text=True)
+        assert v.body().getvalue() == z['plain'] and v.message_complete(), name
+
+
+# ------------------------------------------------------------------------------- config 2 shape
+def test_c2_corpus_parse_matches_oracle(eng):
+    ar = eng.corpus_host(20130725, 0, 60000, 0)
+    g = eng.parse(ar)
+    o = O.orc_parse(ar, hdr_cap=1 << 21)
+    assert_parse_equal(ar, g, o, 'c2 60k')
+    assert (g.code() == N.S_OK).all()
+    eng.set_force_scalar(True)
+    try:
+        g2 = eng.parse(ar)
+    finally:
+        eng.set_force_scalar(False)
+    assert_parse_equal(ar, g2, o, 'c2 60k scalar path')
+
+
+def test_c2_corpus_every_alignment_and_tail(eng):
+    """Messages at all 16 alignments, and truncated at every length around the chunk edges."""
+    rng = np.random.default_rng(2)
+    base = eng.corpus_host(7, 0, 400, 0)
+    msgs = [base.message(i) for i in range(400)]
+    cut = []
+    for m in msgs[:60]:
+        for k in (1, 2, 3, 4, 5, 17, 33):
+            cut.append(m[:len(m) - k])
+        for k in (496, 510, 511, 512, 513, 514, 528):
+            if k < len(m):
+                cut.append(m[:k])
+    ar = scatter_pack(eng, msgs + cut, rng)
+    assert_parse_equal(ar, eng.parse(ar), O.orc_parse(ar), 'alignment + truncation')
+
+
+def test_structural_edge_cases(eng):
+    """Shapes that leave the vector path: long lines, > 32 lines per chunk, whitespace around the
+    header block, lines straddling 512-byte chunks, > 640 records per warp group, 64 KiB limit."""
+    rng = np.random.default_rng(3)
+    msgs = []
+    for n in (300, 500, 511, 512, 513, 1500, 5000):                      # long URL / first line
+        msgs.append(b'GET /' + b'u' * n + b' HTTP/1.1\r\nHost: a\r\nX: y\r\n\r\n')
+    for n in (480, 495, 505, 1020, 3000):                               # long header value
+        msgs.append(b'GET /a HTTP/1.1\r\nHost: a\r\nBig: ' + b'v' * n + b'\r\nAfter: z\r\n\r\n')
+        msgs.append(b'GET /a HTTP/1.1\r\n' + b'K' * n + b': v\r\nAfter: z\r\n\r\n')
+    for n in (20, 31, 32, 33, 34, 64, 65, 100, 200, 641, 700, 2000):     # many short lines
+        msgs.append(b'GET /a HTTP/1.1\r\n' + b''.join(b'a%d: b\r\n' % i for i in range(n)) + b'\r\n')
+        msgs.append(b'HTTP/1.1 200 OK\r\n' + b''.join(b'h: %d\r\n' % i for i in range(n)) + b'Content-Length: 3\r\n\r\nabc')
+    for pad in range(0, 40):                                            # ': ' and CRLF straddling chunk edges
+        msgs.append(b'GET /' + b'p' * (460 + pad) + b' HTTP/1.1\r\nHost: example.org\r\nAccept: */*\r\n\r\n')
+        msgs.append(b'GET /a HTTP/1.1\r\nHost: ' + b'h' * (470 + pad) + b'\r\nA: b\r\nC: d\r\n\r\n')
+    msgs += [b'GET /a HTTP/1.1\r\n \tHost: a\r\nX: y\r\n\r\n', b'GET /a HTTP/1.1\r\nHost: a\r\nX: y \t\r\n\r\n',
+             b'GET /a HTTP/1.1\r\nHost: a\r\nX: \r\n\r\n', b'GET /a HTTP/1.1\r\nHost: a\r\n \r\n\r\n',
+             b'GET /a HTTP/1.1\r\nHost:  a  \r\nX:\ty\r\n\r\n', b'GET /a HTTP/1.1\r\nHost: a: b\r\n\r\n',
+             b'GET /a HTTP/1.1\r\nnocolon\r\nHost: a\r\n\r\n', b'GET /a HTTP/1.1\r\nHost: a\r\nnocolon\r\n',
+             b'POST /a HTTP/1.1\r\nContent-Length: 5\r\nContent-Length: 5\r\n\r\nhello',
+             b'POST /a HTTP/1.1\r\ncontent-LENGTH:   5  \r\n\r\nhello', b'HEAD /a HTTP/1.0\r\nA: b\r\n\r\n',
+             b'GET /a HTTP/1.1\r\nTransfer-Encoding: chunked\r\n\r\n', b'PUT /a HTTP/1.1\r\nTRANSFER-ENCODING: chunked\r\n\r\n0\r\n\r\n']
+    big = b'GET /a HTTP/1.1\r\n' + b''.join(b'Header-%05d: %s\r\n' % (i, b'v' * 40) for i in range(1165)) + b'\r\n'
+    assert 65000 < len(big) < 65536
+    msgs += [big, big[:-2] + b'X: ' + b'y' * 400 + b'\r\n\r\n']              # just under / over the 64 KiB limit
+    msgs += [m + b'GET /next HTTP/1.1\r\nA: b\r\n\r\n' for m in msgs[:20]]   # pipelined tails
+    order = rng.permutation(len(msgs))
+    ar = scatter_pack(eng, [msgs[i] for i in order], rng)
+    g, o = eng.parse(ar), O.orc_parse(ar)
+    assert_parse_equal(ar, g, o, 'structural edge cases')
+    assert (g.code() == N.E_LIB_HDR_TOO_LARGE).sum() == 1
+    assert_frame_equal(ar, eng.frame(ar, g, reuse_arena=True), O.orc_frame(ar, o), 'edge frame')
+
+
+def test_empty_and_tiny_batches(eng):
+    for msgs in ([b''], [b'', b'', b''], [b'G'], [b'\r\n'], [b'GET / HTTP/1.1\r\nA: b\r\n\r\n'] * 33):
+        ar = eng.pack(msgs)
+        assert_parse_equal(ar, eng.parse(ar), O.orc_parse(ar), repr(msgs[:1]))
+
+
+# ------------------------------------------------------------------------------- config 3 shape
+def _response_corpus(rng, n, lo=4096, hi=1 << 20):
+    msgs = []
+    exts = [b'', b'', b'', b'', b'', b'', b'', b'', b'', b';ext=foo', b';ext="foo"', b';ext=foo7']
+    for i in range(n):
+        size = int(np.exp(rng.uniform(np.log(lo), np.log(hi))))
+        body = rng.integers(0, 256, size, dtype=np.uint8).tobytes()
+        first = [b'HTTP/1.1 200 OK\r\n', b'HTTP/1.1 302 Not Modified\r\n', b'HTTP/1.1 500 Internal Server Error\r\n'][i % 3]
+        hdrs = b''.join(b'X-H%d: %s\r\n' % (k, b'v' * int(rng.integers(1, 40))) for k in range(int(rng.integers(3, 11))))
+        if i % 2 == 0:
+            msgs.append(first + hdrs + b'Content-Length: %d\r\n\r\n' % size + body)
+        else:
+            out, p = [], 0
+            while p < size:
+                c = min(int(rng.integers(512, 16385)), size - p)
+                hx = (b'%x' if rng.random() < 0.5 else b'%X') % c
+                out.append(hx + exts[int(rng.integers(0, len(exts)))] + b'\r\n' + body[p:p + c] + b'\r\n')
+                p += c
+            out.append(b'0\r\n\r\n')
+            msgs.append(first + hdrs + b'Transfer-Encoding: chunked\r\n\r\n' + b''.join(out))
+    return msgs
+
+
+def test_c3_responses_framing(eng):
+    """Config 3: Content-Length and chunked bodies, 4 KiB - 1 MiB; complete and truncated."""
+    rng = np.random.default_rng(20130726)
+    msgs = _response_corpus(rng, 96)
+    msgs += [m[:int(rng.integers(1, len(m)))] for m in msgs[:48]]            # truncated anywhere
+    ar = scatter_pack(eng, msgs, rng)
+    g, o = eng.parse(ar), O.orc_parse(ar)
+    assert_parse_equal(ar, g, o, 'c3 parse')
+    gf, of = eng.frame(ar, g, reuse_arena=True), O.orc_frame(ar, o)
+    assert_frame_equal(ar, gf, of, 'c3 frame')
+    # round trip: de-chunked body == the bytes that were chunked (size-independent property)
+    for i in range(0, 96, 7):
+        v = MessageView(ar.message(i), g, i, gf)
+        assert v.message_complete()
+        assert len(v.raw_body()) == (int(gf.body_bytes[i]) if v.chunked() else v.content_len())
+
+
+def test_chunk_header_primitive(eng):
+    cases = [b'A;ext=foo\r\nAAAA', b'\r\n8;ext="foo"\r\nB', b'0\r\n\r\n', b'zz\r\n', b'0x1f\r\n', b'5', b' 5\r\n', b'',
+             b'ffffffffffffffffffff\r\n', b'1;a=b;c=d\r\n', b'1;a="b\r\n', b'1;a=b"\r\n', b'1;a=""\r\n', b'\r\n\r\n5\r\n']
+    ar = eng.pack(cases)
+    hl, sz, ok = eng.chunk_header(ar)
+    ohl, osz, ook = O.orc_chunk_header(ar)
+    assert hl.tolist() == ohl.tolist() and sz.tolist() == osz.tolist() and ok.tolist() == ook.tolist()
+
+
+# ------------------------------------------------------------------------------- placement
+def test_md5_and_placement_golden(eng, placement_golden):
+    keys = [k.encode('latin-1') for k in placement_golden['keys']]
+    rng = np.random.default_rng(4)
+    ar = scatter_pack(eng, keys, rng)
+    for name, r in placement_golden['rings'].items():
+        eng.ring_build(r['hosts'], r['ports'], r['weights'], r['mode'])
+        vals, nodes = eng.ring_export()
+        ov, on = O.orc_ring(r['hosts'], r['ports'], r['weights'], r['mode'])
+        assert (vals == ov).all() and (nodes == on).all() and len(vals) == r['n_points'], name
+        out = eng.place(ar)
+        assert [out.digest(i).hex() for i in range(len(keys))] == placement_golden['md5'], name
+        assert out.hash[:len(keys)].tolist() == r['hash'], name
+        assert out.node[:len(keys)].tolist() == r['node'], name
+        assert out.hist.tolist() == np.bincount(r['node'], minlength=len(r['hosts'])).tolist(), name
+
+
+def test_md5_all_lengths_and_alignments(eng):
+    rng = np.random.default_rng(5)
+    keys = [rng.integers(0, 256, n, dtype=np.uint8).tobytes() for n in list(range(0, 200)) + [250, 251, 255, 256, 257, 1000, 4096]]
+    eng.ring_build(['10.0.0.%d' % (i + 1) for i in range(16)])
+    for rep in range(4):
+        ar = scatter_pack(eng, keys, rng)
+        out = eng.place(ar)
+        for i, k in enumerate(keys):
+            assert out.digest(i) == hashlib.md5(k).digest(), (rep, len(k))
+
+
+def test_route_fused_matches_parse_then_place(eng, golden):
+    """shl_route_batch == shl_parse_batch + (key = url()) + shl_place_batch == oracle."""
+    hosts = ['10.0.0.%d' % (i + 1) for i in range(16)]
+    eng.ring_build(hosts)
+    vals, nodes = O.orc_ring(hosts, [11211] * 16)
+    rng = np.random.default_rng(6)
+    c2 = eng.corpus_host(20130725, 1000, 5000, 0)
+    msgs = [c2.message(i) for i in range(5000)] + [w['msg'] for w in golden['whole']]
+    ar = scatter_pack(eng, msgs, rng)
+    n = ar.n
+    pg, qg = eng.route(ar)
+    o = O.orc_parse(ar)
+    assert_parse_equal(ar, pg, o, 'route parse fields')
+    st = o.status[:n]
+    routable = ((st & N.F_MESSAGE_COMPLETE) != 0) & ((st & N.F_IS_REQUEST) != 0) & ((st & N.F_FIRST_LINE_DONE) != 0) & ((st & 0xff) == 0)
+    assert routable.sum() > 5000
+    koff = (ar.off + o.sp1[:n] + 1).astype(np.uint64)
+    klen = (o.sp2[:n] - o.sp1[:n] - 1).astype(np.uint32)
+    koff[~routable] = 0
+    klen[~routable] = 0
+    oq = O.orc_place(ar, vals, nodes, 16, np.ascontiguousarray(koff), np.ascontiguousarray(klen))
+    r = routable
+    assert (qg.hash[:n][r] == oq.hash[:n][r]).all()
+    assert (qg.node[:n][r] == oq.node[:n][r]).all()
+    assert (qg.md5[:16 * n].reshape(n, 16)[r] == oq.md5[:16 * n].reshape(n, 16)[r]).all()
+    assert (qg.node[:n][~r] == 0xffffffff).all() and (qg.hash[:n][~r] == 0).all()
+    assert qg.hist.tolist() == np.bincount(oq.node[:n][r], minlength=16).tolist()
+    # the separate entry point agrees with the fused one
+    ks = eng.place(ar, np.ascontiguousarray(koff[r]), np.ascontiguousarray(klen[r]))
+    assert (ks.node[:int(r.sum())] == qg.node[:n][r]).all()
+
+
+def test_c2_full_size_properties(eng):
+    """BASELINE config 2 at full size (1 M GETs, 16x100 ring): size-independent properties plus a
+    full comparison with the oracle (the C oracle finishes 1 M messages in seconds)."""
+    n = 1 << 20
+    hosts = ['10.0.0.%d' % (i + 1) for i in range(16)]
+    eng.ring_build(hosts)
+    ar = eng.corpus_host(20130725, 0, n, 0)
+    pg, qg = eng.route(ar, hdr_cap=1 << 25)
+    assert (pg.code() == N.S_OK).all()
+    assert int(qg.hist.sum()) == n                                    # every request placed exactly once
+    assert (pg.first_line_len[:n] + pg.headers_len[:n] == ar.len).all()
+    assert int(pg.n_headers[:n].sum()) == int(pg.hdr_used[0])
+    hist = eng.code_hist()
+    assert int(hist[N.S_OK]) >= n
+    o = O.orc_parse(ar, hdr_cap=1 << 25)
+    assert_parse_equal(ar, pg, o, 'c2 1M')
+    vals, nodes = O.orc_ring(hosts, [11211] * 16)
+    koff = (ar.off + o.sp1[:n] + 1).astype(np.uint64)
+    klen = (o.sp2[:n] - o.sp1[:n] - 1).astype(np.uint32)
+    oq = O.orc_place(ar, vals, nodes, 16, koff, klen)
+    assert (qg.node[:n] == oq.node[:n]).all() and (qg.hash[:n] == oq.hash[:n]).all()
+    assert (qg.md5[:16 * n] == oq.md5[:16 * n]).all()
+    assert qg.hist.tolist() == oq.hist.tolist()

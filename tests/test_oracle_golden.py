@@ -103,3 +103,45 @@ def test_oracle_chunk_header_primitive():
     hl, sz, ok = O.orc_chunk_header(ar)
     for i, (_, ehl, esz, eok) in enumerate(cases):
         assert (int(hl[i]), int(sz[i]), int(ok[i])) == (ehl, esz, eok), cases[i]
+
+
+# ----------------------------------------------------------------------------- oracle/py_port.py
+def _port_observation(p, calls, exc):
+    def t(x):
+        return x.decode('latin-1') if isinstance(x, bytes) else x
+    hd = {t(k): ([t(x) for x in v] if isinstance(v, list) else t(v)) for k, v in p.headers.items()}
+    return {'calls': calls, 'exc': exc, 'is_request': p.is_request, 'method': t(p.method), 'url': t(p.url),
+            'version': repr(p.version) if p.version is not None else None, 'status': p.status,
+            'message': t(p.reason), 'headers': hd, 'headers_complete': p.headers_complete,
+            'message_complete': p.message_complete, 'chunked': p.chunked, 'content_len': p.content_len,
+            'body': p.body.getvalue().decode('latin-1')}
+
+
+def test_py_port_matches_reference_golden(golden):
+    import sys, os
+    sys.path.insert(0, os.path.join(O.ROOT, 'oracle'))
+    import py_port
+    bad = []
+    for w in golden['whole']:
+        p, calls, exc = py_port.drive(w['msg'].encode('latin-1'))
+        got = _port_observation(p, calls, exc)
+        d = {k: (got[k], w['obs'][k]) for k in got if got[k] != w['obs'][k]}
+        if d:
+            bad.append((w['id'], w['msg'][:80], d))
+    assert not bad, (len(bad), bad[:3])
+    for name, z in golden['gzip'].items():
+        p, calls, exc = py_port.drive(z['msg'].encode('latin-1'))
+        assert exc is None and p.message_complete and p.body.getvalue().decode() == z['plain']
+
+
+def test_py_port_placement_matches_golden(placement_golden):
+    import sys, os
+    sys.path.insert(0, os.path.join(O.ROOT, 'oracle'))
+    import py_port
+    for name, r in placement_golden['rings'].items():
+        if r['n_points'] > 5000:
+            continue
+        values, nodes = py_port.build_ring(r['hosts'], r['ports'], r['weights'], r['mode'])
+        assert len(values) == r['n_points']
+        got = [py_port.place(values, nodes, len(r['hosts']), k.encode('latin-1')) for k in placement_golden['keys']]
+        assert got == r['node'], name
