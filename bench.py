@@ -321,6 +321,8 @@ def run_ours(args):
     k_ms = float(np.mean(kms))
 
     # ---- check the resident result (outside the timed region): histogram adds up
+    step_resident()
+    barrier()
     hs = np.zeros(n_stat, np.uint64)
     eng.d2h(hs, d_stats); eng.sync()
     total_hdrs = np.zeros(1, np.uint64)
