@@ -45,6 +45,12 @@ class Engine(object):
         a[:] = 0
         return a.view(dt)
 
+    def release_pinned(self, mark):
+        """Free every pinned array allocated after `mark = len(self._pinned)` (the arrays die)."""
+        self.sync()
+        while len(self._pinned) > mark:
+            self.lib.shl_pinned_free(self._pinned.pop())
+
     def pack(self, messages, align=1):
         return Arena.pack(messages, alloc=self.pinned, align=align)
 

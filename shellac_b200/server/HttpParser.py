@@ -1,0 +1,386 @@
+"""HttpParser — the reference's class and method surface (HttpParser.py:43-351) over the device path.
+
+    p = HttpParser()
+    while not p.message_complete():
+        c = p.parse(buf, len(buf))
+        buf = buf[c:]
+    p.headers(); p.body().read()
+
+Same constructor, same `parse(data, length)` return values per call (`None` for length 0), same
+getters, same exception TYPES at the same call.  The boundaries (first CRLF, CRLFCRLF, first-line
+fields, header spans, chunk headers) come from the CUDA kernels through the C ABI; this class only
+keeps the reference's per-connection buffering (HttpParser.py:153,174,209,247) and turns spans into
+Python objects.  There is no CPU parser behind it: without the library / a GPU it raises.
+
+`HttpParser.parse_many(messages)` is the batch entry: one device call for the whole list.
+
+Type rule: feed `str` and the getters return `str` (latin-1), feed `bytes` and they return `bytes`
+(a Python-2 `str` is bytes; the reference predates the split).
+"""
+import io
+import zlib
+
+from .. import _native as N
+from ..batch import MessageView
+
+_FIRST_LINE_ERRORS = (N.E_FIRSTLINE_PARTS, N.E_VERSION_SPLIT, N.E_VERSION_FLOAT, N.E_STATUS_INT)
+
+
+class DeviceBackend(object):
+    """Runs single buffers through an Engine, reusing one pinned staging area."""
+
+    def __init__(self, engine=None):
+        if engine is None:
+            from ..engine import Engine
+            engine = Engine(device=0, max_msgs=1 << 12, max_bytes=1 << 26)
+        self.eng = engine
+
+    def views(self, bufs, frame=False):
+        """MessageView per buffer (bytes).  The views own copies, the pinned scratch is released."""
+        eng = self.eng
+        mark = len(eng._pinned)
+        try:
+            ar = eng.pack(bufs)
+            po = eng.parse(ar)
+            fo = eng.frame(ar, po, reuse_arena=True) if frame else None
+            out = [MessageView(bufs[i], _Row(po, i), 0, _FrameRow(fo, i) if fo is not None else None)
+                   for i in range(len(bufs))]
+        finally:
+            eng.release_pinned(mark)
+        return out
+
+    def chunk_header(self, buf):
+        eng = self.eng
+        mark = len(eng._pinned)
+        try:
+            hl, sz, ok = eng.chunk_header(eng.pack([buf]))
+            return int(hl[0]), int(sz[0]), bool(ok[0])
+        finally:
+            eng.release_pinned(mark)
+
+
+class _Row(object):
+    """One message's slice of a ParseOut, detached from the pinned arrays."""
+
+    def __init__(self, po, i):
+        for name, _ in N.PARSE_FIELDS:
+            setattr(self, name, [getattr(po, name)[i].item()])
+        b, n = int(po.hdr_base[i]), int(po.n_headers[i])
+        self.hdr = po.hdr[b:b + n].copy()
+        self.hdr_base = [0]
+
+
+class _FrameRow(object):
+    def __init__(self, fo, i):
+        for name, _ in N.FRAME_FIELDS:
+            setattr(self, name, [getattr(fo, name)[i].item()])
+        b, n = int(fo.chunk_base[i]), int(fo.n_chunks[i])
+        self.chunk = fo.chunk[b:b + n].copy()
+        self.chunk_base = [0]
+
+
+_default_backend = None
+
+
+def default_backend():
+    global _default_backend
+    if _default_backend is None:
+        _default_backend = DeviceBackend()
+    return _default_backend
+
+
+def set_default_backend(backend):
+    """Tests on a machine without a GPU inject an oracle-backed backend here; the product never does."""
+    global _default_backend
+    _default_backend = backend
+
+
+class HttpParser(object):
+
+    def __init__(self, backend=None):
+        self._backend = backend
+        self._method = self._version = self._url = self._status = self._message = None
+        self._headers = {}
+        self._body = None
+        self._buf = b''
+        self._line = b''                  # the consumed first line: the device re-reads it with the headers
+        self._is_request = True
+        self._content_len = None
+        self._chunked = False
+        self._text = True
+        self._inflate = zlib.decompressobj(31)            # HttpParser.py:58
+        self._on_first_line, self._on_headers, self._on_body = True, False, False
+        self._headers_complete = self._message_complete = False
+
+    # ------------------------------------------------------------------ getters (HttpParser.py:67-109)
+    def _be(self):
+        return self._backend or default_backend()
+
+    def _t(self, b):
+        if b is None or not isinstance(b, (bytes, bytearray)):
+            return b
+        return bytes(b).decode('latin-1') if self._text else bytes(b)
+
+    def method(self):
+        return self._t(self._method)
+
+    def url(self):
+        return self._t(self._url)
+
+    def status(self):
+        return self._status
+
+    def version(self):
+        return self._version
+
+    def message(self):
+        return self._t(self._message)
+
+    def headers(self):
+        return self._headers
+
+    def body(self):
+        if self._body is None:
+            self._body = io.StringIO() if self._text else io.BytesIO()
+        return self._body
+
+    def is_request(self):
+        return self._is_request
+
+    def is_response(self):
+        return not self._is_request
+
+    def headers_complete(self):
+        return self._headers_complete
+
+    def message_complete(self):
+        return self._message_complete
+
+    def _lit(self, s):
+        return s if self._text else s.encode('latin-1')
+
+    def keep_alive(self):
+        return self._headers.get(self._lit('connection'), self._lit('close')).lower() == self._lit('keep-alive')
+
+    def keep_alive_params(self):
+        if not self.keep_alive():
+            return (0, 1)
+        ka = self._headers.get(self._lit('keep-alive'), self._lit('timeout=5, max=100'))
+        kp = {}
+        for item in ka.split(self._lit(', ')):
+            k, v = item.split(self._lit('='))
+            kp[k] = int(v)
+        return (kp.get(self._lit('timeout'), 5), kp.get(self._lit('max'), 100))
+
+    # ------------------------------------------------------------------ re-serialisation (HttpParser.py:111-138)
+    def serialize(self):
+        """The bytes `str(parser)` yields in the reference.  Header ORDER there is Python-2 dict
+        hash order (HttpParser.py:23,136) and not reproducible; here it is arrival order."""
+        L = lambda s: s.encode('latin-1') if isinstance(s, str) else s          # noqa: E731
+        if self.is_request():
+            s = b'%s %s HTTP/%s\r\n' % (L(self.method()), L(self.url()), b'%.1f' % self.version())
+        else:
+            s = b'HTTP/%s %d %s\r\n' % (b'%.1f' % self.version(), self.status(), L(self.message()))
+        self._headers.pop(self._lit('transfer-encoding'), None)
+        self._headers.pop(self._lit('content-length'), None)
+        body = self.body()
+        body.seek(0)
+        b = L(body.read())
+        if self._headers.get(self._lit('content-encoding'), self._lit('identity')) == self._lit('gzip'):
+            zz = zlib.compressobj(6, zlib.DEFLATED, 31)
+            b = zz.compress(b) + zz.flush()
+        if len(b) != 0:
+            self._headers[self._lit('content-length')] = len(b)
+        h = b''
+        for k, v in self._headers.items():
+            name = b'-'.join(x.capitalize() for x in L(k).split(b'-'))
+            if isinstance(v, list):
+                val = b', '.join(L(x) for x in v)
+            else:
+                val = L(v) if isinstance(v, (str, bytes)) else b'%d' % v
+            h += name + b': ' + val + b'\r\n'
+        return s + h + b'\r\n' + b
+
+    def __str__(self):
+        return self.serialize().decode('latin-1')
+
+    # ------------------------------------------------------------------ parse (HttpParser.py:140-232)
+    def parse(self, data, length):
+        """Parse data, return number of bytes consumed."""
+        if length == 0:
+            return None
+        if isinstance(data, str):
+            data = data.encode('latin-1')
+        else:
+            self._text = False
+        if self._on_first_line:
+            return self._parse_line(data, length)
+        if self._on_headers:
+            return self._parse_headers(data, length)
+        if self._on_body:
+            if self._chunked:
+                return self._parse_chunked(data, length)
+            return self._parse_sized(data, length)
+        return 0
+
+    def _parse_line(self, data, length):
+        had = len(self._buf)
+        self._buf += data
+        v = self._be().views([self._buf])[0]
+        if v.code in (N.S_INCOMPLETE_LINE, N.S_EMPTY):
+            return length                                                   # :156-157
+        fl = int(v.p.first_line_len[0])
+        self._buf = self._buf[:fl]                                          # :159
+        self._is_request = v.is_request()
+        self._version = v.version()
+        if v.code in _FIRST_LINE_ERRORS:
+            raise ValueError('malformed first line (%s)' % N.CODE_NAMES[v.code])   # :307-319
+        self._method, self._url = v.method(), v.url()
+        self._status, self._message = v.status(), v.message()
+        self._line, self._buf = self._buf, b''
+        self._on_first_line, self._on_headers = False, True
+        return fl - had                                                     # :163
+
+    def _parse_headers(self, data, length):
+        had = len(self._buf)
+        self._buf += data
+        v = self._be().views([self._line + self._buf])[0]
+        if v.code == N.S_INCOMPLETE_HEADERS:
+            return length                                                   # :177-178
+        if v.code == N.E_LIB_HDR_TOO_LARGE:
+            raise OverflowError('header block beyond 64 KiB (library limit)')
+        hl = int(v.p.headers_len[0])
+        self._buf = self._buf[:hl]                                          # :180
+        v.text = self._text
+        for k, val in v.header_items():                                     # :327-337
+            if k in self._headers:
+                if isinstance(self._headers[k], list):
+                    self._headers[k].append(val)
+                else:
+                    self._headers[k] = [self._headers[k], val]
+            else:
+                self._headers[k] = val
+        if v.code in (N.E_HDR_NO_SEP, N.E_HDR_MULTI_SEP):
+            raise ValueError('malformed header line (%s)' % N.CODE_NAMES[v.code])  # :328
+        self._buf = b''
+        self._headers_complete, self._on_headers, self._on_body = True, False, True
+        if self._method in (b'GET', b'HEAD'):                               # :191
+            self._message_complete = True
+        self._chunked = v.chunked()                                         # :194
+        if not self._chunked:
+            if v.code == N.E_CLEN_INT:
+                raise ValueError('invalid literal for int() in content-length')    # :197
+            if v.code == N.E_CLEN_LIST:
+                raise TypeError('int() argument must be a string, not list')       # :197
+            self._content_len = v.content_len()
+            if self._content_len == 0:                                      # :198-200
+                self._on_body = False
+                self._message_complete = True
+        return hl - had                                                     # :184
+
+    def _parse_sized(self, data, length):                                   # :206-223
+        if length < self._content_len:
+            self._buf += data
+            self._content_len -= length
+            return length
+        self._buf += data[:self._content_len]
+        self._write_body()
+        self._flush_body()
+        self._buf = b''
+        used = self._content_len
+        self._content_len = 0
+        self._on_body = False
+        self._message_complete = True
+        return used
+
+    def _parse_chunked(self, data, length):                                 # :243-301
+        had = len(self._buf)
+        self._buf += data
+        used = 0
+        if self._content_len is None:
+            idx, size, ok = self._be().chunk_header(self._buf)              # CHUNK_HEADER_RX.match, :253
+            if idx < 0:
+                return length
+            if not ok:
+                raise ValueError('invalid literal for int() with base 16')  # :239-241
+            if size >= (1 << 63):        # the device saturates; Python carries the exact long (:239-241)
+                size = int(self._buf[:idx].strip().split(b';')[0], 16)
+            self._content_len = size
+            used = idx - had
+            self._buf = self._buf[idx:]
+            left = len(self._buf)
+            if self._content_len == 0:                                      # :268-276
+                if self._buf.startswith(b'\r\n'):
+                    used += 2
+                    self._flush_body()
+                    self._on_body = False
+                    self._message_complete = True
+                self._buf = b''
+                return used
+        elif self._content_len == 0:                                        # :278-287
+            if self._buf.startswith(b'\r\n'):
+                used = 2 - had
+                self._flush_body()
+                self._buf = b''
+                self._on_body = False
+                self._message_complete = True
+                return used
+            return length
+        else:
+            left = length
+        if left < self._content_len:                                        # :291-294
+            self._content_len -= left
+            return used + left
+        self._buf = self._buf[:had + self._content_len]                     # :296 (stale `had` quirk kept)
+        self._write_body()
+        self._buf = b''
+        used += self._content_len
+        self._content_len = None
+        return used
+
+    # ------------------------------------------------------------------ body sink (HttpParser.py:340-351)
+    def _gzip(self):
+        return self._headers.get(self._lit('content-encoding'), self._lit('identity')) == self._lit('gzip')
+
+    def _emit(self, raw):
+        body = self.body()
+        pos = body.tell()
+        body.seek(0, 2)
+        body.write(raw.decode('latin-1') if self._text else raw)
+        body.seek(pos)
+
+    def _write_body(self):
+        self._emit(self._inflate.decompress(self._buf) if self._gzip() else self._buf)
+
+    def _flush_body(self):
+        if self._gzip():
+            self._emit(self._inflate.flush())
+
+    # ------------------------------------------------------------------ batch entry
+    @classmethod
+    def parse_many(cls, messages, backend=None):
+        """One device call for a list of whole messages; returns a parser object per message in
+        the state the reference object is in after being driven over that message.  A message
+        whose parse raised in the reference carries the exception in `.error` instead."""
+        be = backend or default_backend()
+        text = [isinstance(m, str) for m in messages]
+        bufs = [m.encode('latin-1') if isinstance(m, str) else bytes(m) for m in messages]
+        out = []
+        for v, is_text in zip(be.views(bufs, frame=True), text):
+            v.text = is_text
+            p = cls(backend=be)
+            p._text = is_text
+            p._is_request, p._version = v.is_request(), v.version()
+            un = (lambda x: x.encode('latin-1') if isinstance(x, str) else x)
+            p._method, p._url, p._message, p._status = un(v.method()), un(v.url()), un(v.message()), v.status()
+            p._headers = v.headers()
+            p._headers_complete, p._message_complete = v.headers_complete(), v.message_complete()
+            p._chunked, p._on_body = v.chunked(), v.on_body()
+            p._on_first_line = not (v.st & N.F_FIRST_LINE_DONE)
+            p._on_headers = bool(v.st & N.F_FIRST_LINE_DONE) and not p._headers_complete
+            p._body = v.body()
+            p.calls = v.calls()
+            exc = v.exception()
+            p.error = exc() if exc else None
+            out.append(p)
+        return out
