@@ -216,6 +216,29 @@ int  shl_place_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_key_o
 int  shl_route_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_off, const uint32_t* d_len,
                    uint64_t n, const shl_parse_out* d_pout, const shl_place_out* d_qout);
 
+/* Placement without any allocation.  It has no counterpart in the reference: it exists for callers
+ * of THIS library that cannot call cudaMalloc (the proxy's reactor thread, where an allocation
+ * would take the driver's device-wide lock and stall every batch in flight; a one-off "which node
+ * owns this key?" probe in a process that never created a ctx; a GPU whose memory is already fully
+ * handed out, where an allocation can fail at run time).  Same results as shl_place_batch, but no
+ * ctx: keys and ring come in as HOST arrays (the ring as shl_ring_export returns it), results go
+ * to HOST arrays (any of md5/hash/node/hist may be NULL; hist is ADDED to), and the device-side
+ * working memory is one fixed array inside the library (about 536 KiB held on every GPU that loads
+ * it, until the process exits).  Sizes beyond the SHL_STATIC_MAX_* limits are refused with
+ * SHL_ERR_ARG and a message in shl_last_error(NULL).  The call returns when the results are in
+ * host memory.  The first call on a device also resolves the array's device address; make that
+ * first call before any stream capture starts.  All calls share the array, which still holds the
+ * previous call's data (the histogram bins are cleared each time): calls whose GPU work overlaps
+ * on one device race, so serialise them per device.                                              */
+#define SHL_STATIC_MAX_KEYS       4096
+#define SHL_STATIC_MAX_KEY_BYTES  262144
+#define SHL_STATIC_MAX_POINTS     16384
+#define SHL_STATIC_MAX_HOSTS      1024
+int  shl_place_static(int device, const uint8_t* arena, uint64_t arena_bytes, const uint64_t* key_off,
+                      const uint32_t* key_len, uint64_t n, const uint32_t* ring_values,
+                      const uint32_t* ring_nodes, uint32_t n_points, uint32_t n_hosts,
+                      uint8_t* md5, uint32_t* hash, uint32_t* node, uint64_t* hist);
+
 /* Number of kernel launches this ctx has issued (for bench.py's gpu_launches claim). */
 uint64_t shl_launch_count(shl_ctx* ctx);
 

@@ -119,6 +119,7 @@ def lib():
         'shl_frame_dev': (i32, [vp, vp, vp, vp, u64, vp, vp, vp, C.POINTER(FrameOutStruct)]),
         'shl_place_dev': (i32, [vp, vp, vp, vp, u64, C.POINTER(PlaceOutStruct)]),
         'shl_route_dev': (i32, [vp, vp, vp, vp, u64, C.POINTER(ParseOutStruct), C.POINTER(PlaceOutStruct)]),
+        'shl_place_static': (i32, [i32, vp, u64, vp, vp, u64, vp, vp, C.c_uint32, C.c_uint32, vp, vp, vp, vp]),
         'shl_launch_count': (u64, [vp]),
         'shl_code_hist': (i32, [vp, vp, i32]),
         'shl_code_hist_dev': (vp, [vp]),

@@ -549,3 +549,114 @@ int shl_corpus_fill_dev(shl_ctx* ctx, uint64_t seed, uint64_t first, uint64_t n,
     return SHL_OK;
 }
 }  // extern "C"
+
+// =================================================================================================
+// shl_place_static — placement for callers that must not allocate.
+//
+// Every other entry point works out of buffers that shl_ctx_create / shl_ring_build obtained with
+// cudaMalloc.  Some callers cannot afford that: the proxy's single reactor thread (an allocation
+// takes the driver's device-wide lock and can stall every batch in flight on that GPU), a small
+// "which node owns this key?" probe in a process that never built a ctx, or a deployment where the
+// HBM is already fully handed out to other tenants and an allocation may simply fail at run time.
+// For them the kernel's working memory (staged keys, ring, results, histogram bins) lives in ONE
+// file-scope device array of fixed size that exists from the moment the library is loaded on a
+// GPU until the process exits.  Nothing here calls cudaMalloc, cudaFree or any allocating routine.
+//
+// The array is shared by every call and keeps whatever the previous call left in it; the bins that
+// must start at zero are cleared on every call.  Two calls whose GPU work overlaps on one device
+// would trample each other's keys and results: serialise calls per device.
+// =================================================================================================
+namespace {
+
+constexpr uint64_t kStArena = 0;                                                 // SHL_STATIC_MAX_KEY_BYTES + pad
+constexpr uint64_t kStOff = kStArena + SHL_STATIC_MAX_KEY_BYTES + 256;
+constexpr uint64_t kStLen = kStOff + (uint64_t)SHL_STATIC_MAX_KEYS * 8;
+constexpr uint64_t kStVals = kStLen + (uint64_t)SHL_STATIC_MAX_KEYS * 4;
+constexpr uint64_t kStNodes = kStVals + (uint64_t)SHL_STATIC_MAX_POINTS * 4;
+constexpr uint64_t kStMd5 = kStNodes + (uint64_t)SHL_STATIC_MAX_POINTS * 4;
+constexpr uint64_t kStHash = kStMd5 + (uint64_t)SHL_STATIC_MAX_KEYS * 16;
+constexpr uint64_t kStNode = kStHash + (uint64_t)SHL_STATIC_MAX_KEYS * 4;
+constexpr uint64_t kStHist = kStNode + (uint64_t)SHL_STATIC_MAX_KEYS * 4;
+constexpr uint64_t kStTotal = kStHist + (uint64_t)SHL_STATIC_MAX_HOSTS * 8;
+static_assert(kStOff % 256 == 0 && kStLen % 256 == 0 && kStVals % 256 == 0 && kStNodes % 256 == 0 &&
+              kStMd5 % 256 == 0 && kStHash % 256 == 0 && kStNode % 256 == 0 && kStHist % 256 == 0, "carve-outs stay aligned");
+
+// ~536 KiB per GPU that loads the library.  In HOST code this name is only a stand-in for the
+// symbol, not a device address: it must never be handed to a kernel or a memcpy directly.
+static __device__ __align__(256) uint8_t g_place_scratch[kStTotal];
+
+constexpr int kMaxDevices = 64;
+uint8_t* g_place_scratch_dev[kMaxDevices] = {};      // device address of the array, per device, once resolved
+
+}  // namespace
+
+extern "C" int shl_place_static(int device, const uint8_t* arena, uint64_t arena_bytes, const uint64_t* key_off,
+                                const uint32_t* key_len, uint64_t n, const uint32_t* ring_values,
+                                const uint32_t* ring_nodes, uint32_t n_points, uint32_t n_hosts,
+                                uint8_t* md5, uint32_t* hash, uint32_t* node, uint64_t* hist) {
+    shl_ctx* ctx = nullptr;      // for the CU() macro: errors land in the process-wide last-error text
+    if (!arena || !key_off || !key_len || !ring_values || !ring_nodes)
+        return fail(nullptr, SHL_ERR_ARG, "shl_place_static: null input pointer");
+    char why[200];
+    if (n > SHL_STATIC_MAX_KEYS) {
+        snprintf(why, sizeof why, "shl_place_static: %llu keys exceed SHL_STATIC_MAX_KEYS = %d", (unsigned long long)n, SHL_STATIC_MAX_KEYS);
+        return fail(nullptr, SHL_ERR_ARG, why);
+    }
+    if (arena_bytes > SHL_STATIC_MAX_KEY_BYTES) {
+        snprintf(why, sizeof why, "shl_place_static: %llu key bytes exceed SHL_STATIC_MAX_KEY_BYTES = %d", (unsigned long long)arena_bytes, SHL_STATIC_MAX_KEY_BYTES);
+        return fail(nullptr, SHL_ERR_ARG, why);
+    }
+    if (n_points == 0 || n_points > SHL_STATIC_MAX_POINTS || n_hosts == 0 || n_hosts > SHL_STATIC_MAX_HOSTS) {
+        snprintf(why, sizeof why, "shl_place_static: ring of %u points / %u hosts outside (0, %d] points / (0, %d] hosts",
+                 n_points, n_hosts, SHL_STATIC_MAX_POINTS, SHL_STATIC_MAX_HOSTS);
+        return fail(nullptr, SHL_ERR_ARG, why);
+    }
+    for (uint64_t i = 0; i < n; i++)
+        if (key_off[i] > arena_bytes || key_len[i] > arena_bytes - key_off[i])
+            return fail(nullptr, SHL_ERR_ARG, "shl_place_static: a key lies outside the arena");
+    for (uint32_t i = 0; i < n_points; i++)
+        if (ring_nodes[i] >= n_hosts) return fail(nullptr, SHL_ERR_ARG, "shl_place_static: ring node index >= n_hosts");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(nullptr, SHL_ERR_NO_DEVICE, "no CUDA device: libshellac_b200 has no CPU fallback");
+    if (device < 0 || device >= ndev || device >= kMaxDevices) return fail(nullptr, SHL_ERR_ARG, "shl_place_static: bad device index");
+    CU(cudaSetDevice(device));
+    // Set-up, once per device and with that device current: ask the runtime where THIS device's
+    // copy of the array lives.  The first call on a device does it, so make that first call
+    // before any stream capture begins.
+    uint8_t* base = g_place_scratch_dev[device];
+    if (!base) {
+        CU(cudaGetSymbolAddress(reinterpret_cast<void**>(&base), g_place_scratch));
+        g_place_scratch_dev[device] = base;
+    }
+    if (n == 0) return SHL_OK;
+    const cudaStream_t st = 0;                           // the device's default stream
+    CU(cudaMemcpyAsync(base + kStArena, arena, arena_bytes, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(base + kStOff, key_off, n * 8, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(base + kStLen, key_len, n * 4, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(base + kStVals, ring_values, (size_t)n_points * 4, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(base + kStNodes, ring_nodes, (size_t)n_points * 4, cudaMemcpyHostToDevice, st));
+    CU(cudaMemsetAsync(base + kStHist, 0, (size_t)n_hosts * 8, st));     // the bins are the one thing that must start at zero
+    shl::PlaceArgs a{};
+    a.arena = base + kStArena;
+    a.key_off = reinterpret_cast<const uint64_t*>(base + kStOff);
+    a.key_len = reinterpret_cast<const uint32_t*>(base + kStLen);
+    a.n = n;
+    a.ring_values = reinterpret_cast<const uint32_t*>(base + kStVals);
+    a.ring_nodes = reinterpret_cast<const uint32_t*>(base + kStNodes);
+    a.n_points = n_points; a.n_hosts = n_hosts;
+    a.out.md5 = base + kStMd5;
+    a.out.hash = reinterpret_cast<uint32_t*>(base + kStHash);
+    a.out.node = reinterpret_cast<uint32_t*>(base + kStNode);
+    a.out.hist = reinterpret_cast<uint64_t*>(base + kStHist);
+    shl::k_place<<<(unsigned)((n + 255) / 256), 256, (size_t)n_hosts * 4, st>>>(a);
+    CU(cudaGetLastError());
+    uint64_t bins[SHL_STATIC_MAX_HOSTS];                 // on the stack: no host allocation either
+    if (md5) CU(cudaMemcpyAsync(md5, base + kStMd5, n * 16, cudaMemcpyDeviceToHost, st));
+    if (hash) CU(cudaMemcpyAsync(hash, base + kStHash, n * 4, cudaMemcpyDeviceToHost, st));
+    if (node) CU(cudaMemcpyAsync(node, base + kStNode, n * 4, cudaMemcpyDeviceToHost, st));
+    if (hist) CU(cudaMemcpyAsync(bins, base + kStHist, (size_t)n_hosts * 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (hist) for (uint32_t i = 0; i < n_hosts; i++) hist[i] += bins[i];
+    return SHL_OK;
+}
