@@ -309,8 +309,8 @@ int shl_ring_export(shl_ctx* ctx, uint32_t* values, uint32_t* nodes, uint32_t ca
 
 // ------------------------------------------------------------------------------------ device entry points
 static int check_arena(shl_ctx* ctx, const void* arena) {
-    if ((reinterpret_cast<uintptr_t>(arena) & 15) != 0)
-        return fail(ctx, SHL_ERR_ARG, "arena base must be 16-byte aligned (and padded by 16 readable bytes)");
+    if ((reinterpret_cast<uintptr_t>(arena) & 31) != 0)
+        return fail(ctx, SHL_ERR_ARG, "arena base must be 32-byte aligned (and padded by 64 readable bytes)");
     return SHL_OK;
 }
 
@@ -323,6 +323,7 @@ static int launch_route(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_
     shl::RouteArgs a{};
     a.arena = d_arena; a.off = d_off; a.len = d_len; a.n = n; a.out = *d_out;
     a.code_hist = ctx->d_counters + 2; a.force_scalar = ctx->force_scalar;
+    a.k = shl::swar_host_consts();
     const uint64_t groups = (n + shl::kGroup - 1) / shl::kGroup;
     const unsigned blocks = (unsigned)((groups + shl::kWarpsPerBlock - 1) / shl::kWarpsPerBlock);
     if (d_q) {

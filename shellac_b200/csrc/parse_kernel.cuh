@@ -39,40 +39,49 @@ struct Msg {                          // per-lane result of one message
     int64_t content_len;
 };
 
-struct RouteArgs {
-    const uint8_t* arena; const uint64_t* off; const uint32_t* len; uint64_t n;
-    shl_parse_out out; uint64_t* code_hist;
-    int force_scalar;                 // test hook: take the scalar path for every message
-    // fused placement (route); ring_values == nullptr -> parse only
-    const uint32_t* ring_values; const uint32_t* ring_nodes; uint32_t n_points, n_hosts;
-    shl_place_out place;
-};
 
 // ----------------------------------------------------------------------------------- SWAR
-struct SwarK { uint32_t m7, hi, cr, lf, col, sp; };
-__device__ __forceinline__ SwarK swar_consts() {
-    SwarK k;   // opaque to the optimiser so LOP3 takes them as register operands (one LOP3 per term)
-    asm("mov.u32 %0, 0x7f7f7f7f;" : "=r"(k.m7));
-    asm("mov.u32 %0, 0x80808080;" : "=r"(k.hi));
-    asm("mov.u32 %0, 0x0d0d0d0d;" : "=r"(k.cr));
-    asm("mov.u32 %0, 0x0a0a0a0a;" : "=r"(k.lf));
-    asm("mov.u32 %0, 0x3a3a3a3a;" : "=r"(k.col));
-    asm("mov.u32 %0, 0x20202020;" : "=r"(k.sp));
+// The replicated byte constants arrive as kernel arguments (RouteArgs::k), not as literals: as
+// run-time values they stay in registers / the constant bank, so `(x ^ c) & m7` is ONE LOP3 and
+// the `+ m7` is an IMAD (x * one + m7) on the FMA pipe.  The scan is bound by the ALU pipe
+// (LOP3/SHF/IADD issue at half rate per scheduler), so every op moved to the FMA pipe counts.
+struct SwarK { uint32_t m7, hi, cr, lf, col, sp, one; };
+
+__host__ __device__ inline SwarK swar_host_consts() {
+    SwarK k;
+    k.m7 = 0x7f7f7f7fu; k.hi = 0x80808080u; k.cr = 0x0d0d0d0du; k.lf = 0x0a0a0a0au;
+    k.col = 0x3a3a3a3au; k.sp = 0x20202020u; k.one = 1u;
     return k;
 }
 // 0x80 in every byte of x that equals the (7-bit) byte replicated in c
 __device__ __forceinline__ uint32_t eqf(uint32_t x, uint32_t c, const SwarK& k) {
-    uint32_t t = ((x ^ c) & k.m7) + k.m7;
+    const uint32_t t = ((x ^ c) & k.m7) * k.one + k.m7;
     return ~(t | x) & k.hi;
 }
-// gather the four 0x80 flags of f into bits 0..3
-__device__ __forceinline__ uint32_t nib(uint32_t f) { return __umulhi(f, 0x02040810u) & 0xfu; }
+// ... restricted to the bytes flagged (0x80) in `also`
+__device__ __forceinline__ uint32_t eqf_and(uint32_t x, uint32_t c, uint32_t also, const SwarK& k) {
+    const uint32_t t = ((x ^ c) & k.m7) * k.one + k.m7;
+    return ~(t | x) & also;
+}
+// gather the 0x80 flags of four words into a 16-bit position mask (bit j = byte j)
 __device__ __forceinline__ uint32_t mask16(uint32_t f0, uint32_t f1, uint32_t f2, uint32_t f3) {
-    return nib(f0) | (nib(f1) << 4) | (nib(f2) << 8) | (nib(f3) << 12);
+    const uint32_t h0 = __umulhi(f0, 0x02040810u) & 0xfu, h1 = __umulhi(f1, 0x02040810u) & 0xfu;
+    const uint32_t h2 = __umulhi(f2, 0x02040810u), h3 = __umulhi(f3, 0x02040810u);   // stray bits land above bit 15
+    return (h3 * 4096u + (h2 * 256u + (h1 * 16u + h0))) & 0xffffu;
 }
 __device__ __forceinline__ int clamp16(int v) { return min(max(v, 0), 16); }
 __device__ __forceinline__ uint32_t below(int k) { return (1u << k) - 1u; }            // k in [0,16]
 __device__ __forceinline__ uint32_t rng16(int lo, int hi) { return below(clamp16(hi)) & ~below(clamp16(lo)); }
+
+struct RouteArgs {
+    const uint8_t* arena; const uint64_t* off; const uint32_t* len; uint64_t n;
+    shl_parse_out out; uint64_t* code_hist;
+    int force_scalar;                 // test hook: take the scalar path for every message
+    SwarK k;                          // SWAR byte constants, as run-time values (see SwarK)
+    // fused placement (route); ring_values == nullptr -> parse only
+    const uint32_t* ring_values; const uint32_t* ring_nodes; uint32_t n_points, n_hosts;
+    shl_place_out place;
+};
 
 // ----------------------------------------------------------------------------------- scalar
 // HttpParser._parse_first_line (HttpParser.py:304-321) on m[0:idx+2).  Warp-uniform.
@@ -183,6 +192,62 @@ __device__ __forceinline__ uint32_t ld32u(const uint8_t* p) {
 }
 
 // ----------------------------------------------------------------------------------- one message, one lane
+// Per-lane scan state (all of it lives in registers once the steps below are inlined).
+struct Scan {
+    int p;                       // message position of byte 0 of the vector being scanned
+    int idx, sp1, sp2, h0, T;    // first CRLF, first two spaces, header start, CRLFCRLF position
+    int line_start, sep_first;
+    uint32_t sep_cnt, n_ev, first_bad, bad_cnt, prev_cr, prev_co;
+};
+
+// One 16-byte vector.  Events (header line ends) are pushed to dst[k * stride] as
+// {key_off = position of the line's first ": ", key_len = number of ": " (0, 1, 2+),
+//  val_off = position of the line's CR}; they are turned into records after the scan.
+__device__ __forceinline__ void scan_vec(Scan& s, const uint4 v, const int L, shl_hdr_span* dst, const int stride,
+                                         const uint32_t cap, const SwarK& K) {
+    const uint32_t cr0 = eqf(v.x, K.cr, K), cr1 = eqf(v.y, K.cr, K), cr2 = eqf(v.z, K.cr, K), cr3 = eqf(v.w, K.cr, K);
+    const uint32_t co0 = eqf(v.x, K.col, K), co1 = eqf(v.y, K.col, K), co2 = eqf(v.z, K.col, K), co3 = eqf(v.w, K.col, K);
+    // "LF preceded by CR" / "' ' preceded by ':'": the predecessor flags shifted up one byte
+    uint32_t c16 = mask16(eqf_and(v.x, K.lf, __funnelshift_l(s.prev_cr, cr0, 8), K), eqf_and(v.y, K.lf, __funnelshift_l(cr0, cr1, 8), K),
+                          eqf_and(v.z, K.lf, __funnelshift_l(cr1, cr2, 8), K), eqf_and(v.w, K.lf, __funnelshift_l(cr2, cr3, 8), K));
+    uint32_t s16 = mask16(eqf_and(v.x, K.sp, __funnelshift_l(s.prev_co, co0, 8), K), eqf_and(v.y, K.sp, __funnelshift_l(co0, co1, 8), K),
+                          eqf_and(v.z, K.sp, __funnelshift_l(co1, co2, 8), K), eqf_and(v.w, K.sp, __funnelshift_l(co2, co3, 8), K));
+    s.prev_cr = cr3; s.prev_co = co3;
+    const int p = s.p;
+    if (p < 1 || p + 16 > L) { const uint32_t vm = rng16(1 - p, L - p); c16 &= vm; s16 &= vm; }
+    if (s.idx < 0) {                               // still on the first line: note its first two spaces
+        uint32_t z = mask16(eqf(v.x, K.sp, K), eqf(v.y, K.sp, K), eqf(v.z, K.sp, K), eqf(v.w, K.sp, K));
+        if (p < 0 || p + 16 > L) z &= rng16(-p, L - p);
+        if (c16) z &= below(__ffs(c16) - 1);
+        if (z && s.sp1 < 0) { s.sp1 = p + __ffs(z) - 1; z &= z - 1u; }
+        if (z && s.sp1 >= 0 && s.sp2 < 0) s.sp2 = p + __ffs(z) - 1;
+    }
+    int lo = 0;
+    while (c16) {
+        const int k = __ffs(c16) - 1;              // the LF; its CR sits at k - 1
+        c16 &= c16 - 1u;
+        const int cr_pos = p + k - 1;
+        const uint32_t seg = s16 & below(k) & ~below(lo);
+        lo = k + 1;
+        if (s.idx < 0) { s.idx = cr_pos; s.h0 = s.line_start = cr_pos + 2; continue; }
+        if (seg) { if (!s.sep_cnt) s.sep_first = p + __ffs(seg) - 2; s.sep_cnt += (uint32_t)__popc(seg); }
+        if (cr_pos == s.line_start && s.line_start > s.h0) { s.T = s.line_start - 2; return; }   // empty line: CRLFCRLF at T
+        if (s.sep_cnt != 1u && s.n_ev < s.first_bad) { s.first_bad = s.n_ev; s.bad_cnt = s.sep_cnt; }
+        if (s.n_ev < cap) {
+            shl_hdr_span ev;
+            ev.key_off = (uint16_t)s.sep_first; ev.key_len = (uint16_t)min(s.sep_cnt, 2u);
+            ev.val_off = (uint16_t)cr_pos; ev.val_len = 0;
+            dst[(size_t)s.n_ev * stride] = ev;
+        }
+        s.n_ev++;
+        s.line_start = cr_pos + 2; s.sep_cnt = 0;
+    }
+    if (s.idx >= 0) {
+        const uint32_t seg = s16 & ~below(lo);
+        if (seg) { if (!s.sep_cnt) s.sep_first = p + __ffs(seg) - 2; s.sep_cnt += (uint32_t)__popc(seg); }
+    }
+}
+
 // Records go to dst[k * stride] for k < cap (shared staging: stride 32; global: stride 1);
 // r.n_headers counts every tokenised line even when cap is smaller (the caller then re-runs the
 // message with exactly that much room in the global record arena).
@@ -193,76 +258,31 @@ __device__ __forceinline__ void scan_message(const uint8_t* m, const int L, shl_
     r.status_code = 0; r.content_len = 0;
     if (L == 0) { r.status |= SHL_S_EMPTY; return; }
 
-    const int lead = (int)(reinterpret_cast<uintptr_t>(m) & 15);
+    // Each lane streams its own message one 32-byte sector (two vectors) per iteration, the next
+    // sector already in flight; the first sector is aligned down and its lead bytes are masked.
+    const int lead = (int)(reinterpret_cast<uintptr_t>(m) & 31);
     const uint4* vp = reinterpret_cast<const uint4*>(m - lead);
-    const int nvec = (lead + L + 15) >> 4;
-    int p = -lead;                                 // message position of byte 0 of the current vector
-    int idx = -1, sp1 = -1, sp2 = -1, h0 = 0, T = -1;
-    int line_start = 0, sep_first = 0;
-    uint32_t sep_cnt = 0, n_hdr = 0, hdr_err = 0, prev_cr = 0, prev_co = 0;
-    bool suspect = false;
-
-    uint4 cur = __ldg(vp);
-    for (int v = 0; v < nvec; v++, p += 16) {
-        const uint4 nxt = (v + 1 < nvec) ? __ldg(vp + v + 1) : make_uint4(0u, 0u, 0u, 0u);
-        // ---- byte classes -> "pair ends here" position masks
-        const uint32_t cr0 = eqf(cur.x, K.cr, K), cr1 = eqf(cur.y, K.cr, K), cr2 = eqf(cur.z, K.cr, K), cr3 = eqf(cur.w, K.cr, K);
-        const uint32_t co0 = eqf(cur.x, K.col, K), co1 = eqf(cur.y, K.col, K), co2 = eqf(cur.z, K.col, K), co3 = eqf(cur.w, K.col, K);
-        const uint32_t sx0 = eqf(cur.x, K.sp, K), sx1 = eqf(cur.y, K.sp, K), sx2 = eqf(cur.z, K.sp, K), sx3 = eqf(cur.w, K.sp, K);
-        uint32_t c16 = mask16(eqf(cur.x, K.lf, K) & __funnelshift_l(prev_cr, cr0, 8), eqf(cur.y, K.lf, K) & __funnelshift_l(cr0, cr1, 8),
-                              eqf(cur.z, K.lf, K) & __funnelshift_l(cr1, cr2, 8), eqf(cur.w, K.lf, K) & __funnelshift_l(cr2, cr3, 8));
-        uint32_t s16 = mask16(sx0 & __funnelshift_l(prev_co, co0, 8), sx1 & __funnelshift_l(co0, co1, 8),
-                              sx2 & __funnelshift_l(co1, co2, 8), sx3 & __funnelshift_l(co2, co3, 8));
-        prev_cr = cr3; prev_co = co3;
-        if (p < 1 || p + 16 > L) { const uint32_t vm = rng16(1 - p, L - p); c16 &= vm; s16 &= vm; }
-        if (idx < 0) {                             // still on the first line: note its first two spaces
-            uint32_t z = mask16(sx0, sx1, sx2, sx3);
-            if (p < 0 || p + 16 > L) z &= rng16(-p, L - p);
-            if (c16) z &= below(__ffs(c16) - 1);
-            if (z && sp1 < 0) { sp1 = p + __ffs(z) - 1; z &= z - 1u; }
-            if (z && sp1 >= 0 && sp2 < 0) sp2 = p + __ffs(z) - 1;
+    const int nsec = (lead + L + 31) >> 5;
+    Scan s;
+    s.p = -lead; s.idx = s.sp1 = s.sp2 = -1; s.h0 = 0; s.T = -1; s.line_start = 0; s.sep_first = 0;
+    s.sep_cnt = 0; s.n_ev = 0; s.first_bad = 0xffffffffu; s.bad_cnt = 0; s.prev_cr = 0; s.prev_co = 0;
+    uint4 a0 = __ldg(vp), a1 = __ldg(vp + 1);
+    for (int i = 0; i < nsec; i++) {
+        uint4 b0 = make_uint4(0u, 0u, 0u, 0u), b1 = b0;
+        if (i + 1 < nsec) { b0 = __ldg(vp + 2 * i + 2); b1 = __ldg(vp + 2 * i + 3); }
+        scan_vec(s, a0, L, dst, stride, cap, K);
+        if (s.T >= 0) break;
+        s.p += 16;
+        if (s.p < L) {
+            scan_vec(s, a1, L, dst, stride, cap, K);
+            if (s.T >= 0) break;
         }
-        int lo = 0;
-        while (c16) {
-            const int k = __ffs(c16) - 1;          // the LF; the CR sits at k - 1
-            c16 &= c16 - 1u;
-            const int cr_pos = p + k - 1;
-            const uint32_t seg = s16 & below(k) & ~below(lo);
-            lo = k + 1;
-            if (idx < 0) { idx = cr_pos; h0 = line_start = cr_pos + 2; continue; }
-            if (seg) { if (!sep_cnt) sep_first = p + __ffs(seg) - 2; sep_cnt += (uint32_t)__popc(seg); }
-            if (cr_pos == line_start && line_start > h0) { T = line_start - 2; break; }   // empty line: CRLFCRLF at T
-            if (!hdr_err) {
-                if (sep_cnt != 1u) hdr_err = sep_cnt ? (uint32_t)SHL_E_HDR_MULTI_SEP : (uint32_t)SHL_E_HDR_NO_SEP;
-                else {
-                    int vs = sep_first + 2, ve = cr_pos;
-                    const uint32_t b0 = vs < ve ? ldb(m + vs) : 'x', b1 = ve > vs ? ldb(m + ve - 1) : 'x';
-                    if (is_ws(b0) || is_ws(b1)) {
-                        while (vs < ve && is_ws(ldb(m + vs))) vs++;
-                        while (ve > vs && is_ws(ldb(m + ve - 1))) ve--;
-                    }
-                    const int klen = sep_first - line_start;
-                    if (n_hdr < cap) {
-                        shl_hdr_span rec;
-                        rec.key_off = (uint16_t)line_start; rec.key_len = (uint16_t)klen;
-                        rec.val_off = (uint16_t)vs; rec.val_len = (uint16_t)(ve - vs);
-                        dst[(size_t)n_hdr * stride] = rec;
-                    }
-                    suspect |= (klen == 14) | (klen == 17);
-                    n_hdr++;
-                }
-            }
-            line_start = cr_pos + 2; sep_cnt = 0;
-        }
-        if (T >= 0) break;
-        if (idx >= 0) {
-            const uint32_t seg = s16 & ~below(lo);
-            if (seg) { if (!sep_cnt) sep_first = p + __ffs(seg) - 2; sep_cnt += (uint32_t)__popc(seg); }
-        }
-        cur = nxt;
+        s.p += 16;
+        a0 = b0; a1 = b1;
     }
 
     // ---- lanes are converged again from here on
+    const int idx = s.idx, sp1 = s.sp1, sp2 = s.sp2, h0 = s.h0, T = s.T;
     if (idx < 0) { r.status |= SHL_S_INCOMPLETE_LINE; return; }
     r.first_line_len = (uint32_t)(idx + 2);
     bool get_or_head = false;
@@ -287,20 +307,39 @@ __device__ __forceinline__ void scan_message(const uint8_t* m, const int L, shl_
     if (T + 4 > 65536) { r.status |= SHL_E_LIB_HDR_TOO_LARGE; return; }
     r.headers_len = (uint32_t)(T + 4 - h0);
     WellKnown wk; wk.n_te = wk.n_cl = 0; wk.te_vs = wk.te_ve = wk.cl_vs = wk.cl_ve = 0;
+    uint32_t n_hdr, hdr_err = 0;
     if (force_scalar || is_ws(ldb(m + h0)) || is_ws(ldb(m + T - 1))) {    // strip() would move the block's ends
         WellKnown w2 = wk; uint32_t n2 = 0;
         hdr_err = headers_scalar(m, h0, T + 4, dst, stride, cap, &n2, &w2);
         wk = w2; n_hdr = n2;
-    } else if (suspect && !hdr_err && n_hdr <= cap) {
-        for (uint32_t k = 0; k < n_hdr; k++) {
-            const shl_hdr_span rec = dst[(size_t)k * stride];
-            const int ko = rec.key_off, vs = rec.val_off, ve = rec.val_off + rec.val_len;
-            if (rec.key_len == 14 && span_eq_lower(m, ko, ko + 14, "content-length")) { if (!wk.n_cl) { wk.cl_vs = vs; wk.cl_ve = ve; } wk.n_cl++; }
-            if (rec.key_len == 17 && span_eq_lower(m, ko, ko + 17, "transfer-encoding")) { if (!wk.n_te) { wk.te_vs = vs; wk.te_ve = ve; } wk.n_te++; }
+    } else {
+        // turn the staged events into records, in place: strip the value, note the two keys that matter
+        n_hdr = min(s.n_ev, s.first_bad);
+        if (s.first_bad < s.n_ev) hdr_err = s.bad_cnt ? (uint32_t)SHL_E_HDR_MULTI_SEP : (uint32_t)SHL_E_HDR_NO_SEP;
+        const uint32_t n_conv = min(n_hdr, cap);
+        int ls = h0;
+        for (uint32_t k = 0; k < n_conv; k++) {
+            const shl_hdr_span ev = dst[(size_t)k * stride];
+            const int sep = ev.key_off, cr = ev.val_off;
+            int vs = sep + 2, ve = cr;
+            const uint32_t c0 = vs < ve ? ldb(m + vs) : 'x', c1 = ve > vs ? ldb(m + ve - 1) : 'x';
+            if (is_ws(c0) || is_ws(c1)) {
+                while (vs < ve && is_ws(ldb(m + vs))) vs++;
+                while (ve > vs && is_ws(ldb(m + ve - 1))) ve--;
+            }
+            const int klen = sep - ls;
+            shl_hdr_span rec;
+            rec.key_off = (uint16_t)ls; rec.key_len = (uint16_t)klen;
+            rec.val_off = (uint16_t)vs; rec.val_len = (uint16_t)(ve - vs);
+            dst[(size_t)k * stride] = rec;
+            if (klen == 14) { if (span_eq_lower(m, ls, sep, "content-length")) { if (!wk.n_cl) { wk.cl_vs = vs; wk.cl_ve = ve; } wk.n_cl++; } }
+            else if (klen == 17) { if (span_eq_lower(m, ls, sep, "transfer-encoding")) { if (!wk.n_te) { wk.te_vs = vs; wk.te_ve = ve; } wk.n_te++; } }
+            ls = cr + 2;
         }
     }
     r.n_headers = n_hdr;
     if (hdr_err) { r.status |= hdr_err; return; }
+    if (n_hdr > cap) return;                       // not all lines were staged: the caller re-runs this message
     finalize_headers(m, L, T + 4, get_or_head, wk, r.status, r.content_len);
 }
 
@@ -312,7 +351,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 8) k_route(const RouteArg
     extern __shared__ uint32_t s_hist[];                       // kPlace: n_hosts bins (when they fit)
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const SwarK K = swar_consts();
+    const SwarK K = a.k;
     if (threadIdx.x < 64) s_codes[threadIdx.x] = 0u;
     const bool smem_hist = kPlace && a.place.hist != nullptr && a.n_hosts <= 4096u;
     if (smem_hist) for (uint32_t i = threadIdx.x; i < a.n_hosts; i += blockDim.x) s_hist[i] = 0u;
