@@ -4,26 +4,24 @@
 // decision (/root/reference/src/python/shellac/server/HttpParser.py:140-223, 304-337), driven
 // over a whole message as the reference's own test loop does (test/HttpParserTests.py:36-39).
 //
-// Mapping (round 1, second design; the first one, a warp per message with ballot/shuffle structure
-// extraction, measured 960 warp-instructions per request and was issue-bound at 6.6 % of the HBM
-// roofline, see profiles/r01/): one warp owns a GROUP of 32 consecutive messages, LANE j owns
-// MESSAGE j.
-//   * each lane streams its own message in 16-byte vectors (aligned down, lead bytes masked,
-//     next vector prefetched) and classifies the bytes with SWAR compares (CR, LF, ':', ' ');
-//     "LF preceded by CR" and "' ' preceded by ':'" become 16-bit position masks, with the
-//     previous vector's last-byte flags carried in two registers;
-//   * a short per-lane loop walks the CRLF bits: the first one ends the request/status line, an
-//     empty line ends the header block, every other one closes a header line whose ': ' count and
-//     first position were accumulated from the mask; the line's key/value spans go to a
-//     lane-interleaved (bank-conflict-free) shared-memory staging area;
-//   * all per-message structure is lane-private: no ballots, shuffles or shared tables in the scan.
-//     Lanes re-converge after the scan for the first-line evaluation, the Content-Length /
-//     Transfer-Encoding decision, one atomic record allocation per group, the copy-out, the
-//     struct-of-arrays stores (lane j == message j, so they are coalesced) and the fused
-//     MD5 + continuum search + shared-memory histogram.
+// Mapping (round 1, third design; profiles/r01/ has the ncu summaries of the earlier ones: a warp
+// per message with ballot/shuffle structure extraction ran 960 warp-instructions per request, a
+// lane per message that handled every line end inside the scan loop ran 406): one warp owns a
+// GROUP of 32 consecutive messages, LANE j owns MESSAGE j.
+//   scan     each lane streams its own message in 32-byte sectors (aligned down, lead bytes
+//            masked, next sector in flight), classifies the bytes with SWAR compares (CR, LF,
+//            ':', ' ') into 16-bit masks "LF preceded by CR" / "' ' preceded by ':'" (the previous
+//            vector's last-byte flags ride in two registers) and does nothing with the set bits
+//            but append their positions to two lane-private, lane-interleaved u16 lists in
+//            shared memory; two consecutive CRLFs after the first line end the scan.  The loop
+//            body that runs under divergence is a dozen instructions.
+//   epilogue lanes are converged again: first-line evaluation, a sorted merge of the two lists
+//            (line k must hold exactly one ": "), one atomic record allocation per group, value
+//            strip + record write, Content-Length / Transfer-Encoding decision, struct-of-arrays
+//            stores (lane j == message j, so they are coalesced), MD5 + continuum search +
+//            shared-memory histogram.
 // Anything off the canonical shape (responses' first line, whitespace around the header block,
-// more header lines than a lane's staging slots) takes a per-lane scalar path with the same
-// semantics.
+// more lines than the lists hold) takes a per-lane scalar path with the same semantics.
 #pragma once
 #include "shl_device.cuh"
 
@@ -31,7 +29,8 @@ namespace shl {
 
 constexpr int kWarpsPerBlock = 4;
 constexpr int kGroup = 32;            // messages per warp (one per lane)
-constexpr int kLaneCap = 20;          // staged header records per lane (5 KB per warp)
+constexpr int kCrCap = 24;            // CRLF positions a lane can list (first line + 23 header lines)
+constexpr int kSepCap = 28;           // ": " positions a lane can list
 
 struct Msg {                          // per-lane result of one message
     uint32_t status, first_line_len, headers_len, sp1, sp2, fl_end, slash, n_headers;
@@ -191,162 +190,99 @@ __device__ __forceinline__ uint32_t ld32u(const uint8_t* p) {
     return __funnelshift_r(lo, hi, sh);
 }
 
-// ----------------------------------------------------------------------------------- one message, one lane
-// Per-lane scan state (all of it lives in registers once the steps below are inlined).
-struct Scan {
-    int p;                       // message position of byte 0 of the vector being scanned
-    int idx, sp1, sp2, h0, T;    // first CRLF, first two spaces, header start, CRLFCRLF position
-    int line_start, sep_first;
-    uint32_t sep_cnt, n_ev, first_bad, bad_cnt, prev_cr, prev_co;
-};
+// ----------------------------------------------------------------------------------- scan: one message, one lane
+struct LaneScan { int idx, T; uint32_t n_c, n_s; bool ovf; };
 
-// One 16-byte vector.  Events (header line ends) are pushed to dst[k * stride] as
-// {key_off = position of the line's first ": ", key_len = number of ": " (0, 1, 2+),
-//  val_off = position of the line's CR}; they are turned into records after the scan.
-__device__ __forceinline__ void scan_vec(Scan& s, const uint4 v, const int L, shl_hdr_span* dst, const int stride,
-                                         const uint32_t cap, const SwarK& K) {
-    const uint32_t cr0 = eqf(v.x, K.cr, K), cr1 = eqf(v.y, K.cr, K), cr2 = eqf(v.z, K.cr, K), cr3 = eqf(v.w, K.cr, K);
-    const uint32_t co0 = eqf(v.x, K.col, K), co1 = eqf(v.y, K.col, K), co2 = eqf(v.z, K.col, K), co3 = eqf(v.w, K.col, K);
-    // "LF preceded by CR" / "' ' preceded by ':'": the predecessor flags shifted up one byte
-    uint32_t c16 = mask16(eqf_and(v.x, K.lf, __funnelshift_l(s.prev_cr, cr0, 8), K), eqf_and(v.y, K.lf, __funnelshift_l(cr0, cr1, 8), K),
-                          eqf_and(v.z, K.lf, __funnelshift_l(cr1, cr2, 8), K), eqf_and(v.w, K.lf, __funnelshift_l(cr2, cr3, 8), K));
-    uint32_t s16 = mask16(eqf_and(v.x, K.sp, __funnelshift_l(s.prev_co, co0, 8), K), eqf_and(v.y, K.sp, __funnelshift_l(co0, co1, 8), K),
-                          eqf_and(v.z, K.sp, __funnelshift_l(co1, co2, 8), K), eqf_and(v.w, K.sp, __funnelshift_l(co2, co3, 8), K));
-    s.prev_cr = cr3; s.prev_co = co3;
-    const int p = s.p;
-    if (p < 1 || p + 16 > L) { const uint32_t vm = rng16(1 - p, L - p); c16 &= vm; s16 &= vm; }
-    if (s.idx < 0) {                               // still on the first line: note its first two spaces
-        uint32_t z = mask16(eqf(v.x, K.sp, K), eqf(v.y, K.sp, K), eqf(v.z, K.sp, K), eqf(v.w, K.sp, K));
-        if (p < 0 || p + 16 > L) z &= rng16(-p, L - p);
-        if (c16) z &= below(__ffs(c16) - 1);
-        if (z && s.sp1 < 0) { s.sp1 = p + __ffs(z) - 1; z &= z - 1u; }
-        if (z && s.sp1 >= 0 && s.sp2 < 0) s.sp2 = p + __ffs(z) - 1;
-    }
-    int lo = 0;
-    while (c16) {
-        const int k = __ffs(c16) - 1;              // the LF; its CR sits at k - 1
-        c16 &= c16 - 1u;
-        const int cr_pos = p + k - 1;
-        const uint32_t seg = s16 & below(k) & ~below(lo);
-        lo = k + 1;
-        if (s.idx < 0) { s.idx = cr_pos; s.h0 = s.line_start = cr_pos + 2; continue; }
-        if (seg) { if (!s.sep_cnt) s.sep_first = p + __ffs(seg) - 2; s.sep_cnt += (uint32_t)__popc(seg); }
-        if (cr_pos == s.line_start && s.line_start > s.h0) { s.T = s.line_start - 2; return; }   // empty line: CRLFCRLF at T
-        if (s.sep_cnt != 1u && s.n_ev < s.first_bad) { s.first_bad = s.n_ev; s.bad_cnt = s.sep_cnt; }
-        if (s.n_ev < cap) {
-            shl_hdr_span ev;
-            ev.key_off = (uint16_t)s.sep_first; ev.key_len = (uint16_t)min(s.sep_cnt, 2u);
-            ev.val_off = (uint16_t)cr_pos; ev.val_len = 0;
-            dst[(size_t)s.n_ev * stride] = ev;
-        }
-        s.n_ev++;
-        s.line_start = cr_pos + 2; s.sep_cnt = 0;
-    }
-    if (s.idx >= 0) {
-        const uint32_t seg = s16 & ~below(lo);
-        if (seg) { if (!s.sep_cnt) s.sep_first = p + __ffs(seg) - 2; s.sep_cnt += (uint32_t)__popc(seg); }
-    }
-}
-
-// Records go to dst[k * stride] for k < cap (shared staging: stride 32; global: stride 1);
-// r.n_headers counts every tokenised line even when cap is smaller (the caller then re-runs the
-// message with exactly that much room in the global record arena).
-__device__ __forceinline__ void scan_message(const uint8_t* m, const int L, shl_hdr_span* dst, const int stride,
-                                             const uint32_t cap, const SwarK& K, const bool force_scalar, Msg& r) {
-    r.status = (3u << SHL_F_VERSION_SHIFT) | SHL_F_IS_REQUEST;
-    r.first_line_len = r.headers_len = r.sp1 = r.sp2 = r.fl_end = r.slash = r.n_headers = 0;
-    r.status_code = 0; r.content_len = 0;
-    if (L == 0) { r.status |= SHL_S_EMPTY; return; }
-
-    // Each lane streams its own message one 32-byte sector (two vectors) per iteration, the next
-    // sector already in flight; the first sector is aligned down and its lead bytes are masked.
+// cr[k * 32] / sp[k * 32]: this lane's slots of the warp's position lists (u16, lane-interleaved).
+__device__ __forceinline__ void scan_lists(const uint8_t* m, const int L, uint16_t* cr, uint16_t* sp, const SwarK& K, LaneScan& o) {
     const int lead = (int)(reinterpret_cast<uintptr_t>(m) & 31);
     const uint4* vp = reinterpret_cast<const uint4*>(m - lead);
     const int nsec = (lead + L + 31) >> 5;
-    Scan s;
-    s.p = -lead; s.idx = s.sp1 = s.sp2 = -1; s.h0 = 0; s.T = -1; s.line_start = 0; s.sep_first = 0;
-    s.sep_cnt = 0; s.n_ev = 0; s.first_bad = 0xffffffffu; s.bad_cnt = 0; s.prev_cr = 0; s.prev_co = 0;
-    uint4 a0 = __ldg(vp), a1 = __ldg(vp + 1);
-    for (int i = 0; i < nsec; i++) {
-        uint4 b0 = make_uint4(0u, 0u, 0u, 0u), b1 = b0;
-        if (i + 1 < nsec) { b0 = __ldg(vp + 2 * i + 2); b1 = __ldg(vp + 2 * i + 3); }
-        scan_vec(s, a0, L, dst, stride, cap, K);
-        if (s.T >= 0) break;
-        s.p += 16;
-        if (s.p < L) {
-            scan_vec(s, a1, L, dst, stride, cap, K);
-            if (s.T >= 0) break;
-        }
-        s.p += 16;
-        a0 = b0; a1 = b1;
-    }
-
-    // ---- lanes are converged again from here on
-    const int idx = s.idx, sp1 = s.sp1, sp2 = s.sp2, h0 = s.h0, T = s.T;
-    if (idx < 0) { r.status |= SHL_S_INCOMPLETE_LINE; return; }
-    r.first_line_len = (uint32_t)(idx + 2);
-    bool get_or_head = false;
-    bool fast = !force_scalar && sp1 >= 0 && sp2 > sp1 && sp2 < idx && idx - sp2 - 1 == 8;
-    if (fast) {                                    // canonical request line: METHOD SP URL SP "HTTP/1.x" CRLF
-        const uint32_t w0 = ld32u(m + sp2 + 1), w1 = ld32u(m + sp2 + 5), f4 = ld32u(m);
-        fast = w0 == 0x50545448u && (w1 == 0x312E312Fu || w1 == 0x302E312Fu) && !((f4 & 0xffffu) == 0x5448u && sp1 >= 2);
-        if (fast) {
-            r.sp1 = (uint32_t)sp1; r.sp2 = (uint32_t)sp2; r.fl_end = (uint32_t)idx; r.slash = (uint32_t)(sp2 + 5);
-            r.status = (r.status & ~SHL_F_VERSION_MASK) | ((w1 >> 24) == '1' ? 1u << SHL_F_VERSION_SHIFT : 0u) | SHL_F_FIRST_LINE_DONE;
-            get_or_head = (sp1 == 3 && (f4 & 0xffffffu) == 0x544547u) || (sp1 == 4 && f4 == 0x44414548u);
-        }
-    }
-    if (!fast) {
-        Msg t = r;                                 // the cold path may keep its copy in local memory
-        bool goh = false;
-        const uint32_t fl_code = first_line_scalar(m, idx, t, goh);
-        r = t; get_or_head = goh;
-        if (fl_code) { r.status |= fl_code; return; }
-    }
-    if (T < 0) { r.status |= SHL_S_INCOMPLETE_HEADERS; return; }
-    if (T + 4 > 65536) { r.status |= SHL_E_LIB_HDR_TOO_LARGE; return; }
-    r.headers_len = (uint32_t)(T + 4 - h0);
-    WellKnown wk; wk.n_te = wk.n_cl = 0; wk.te_vs = wk.te_ve = wk.cl_vs = wk.cl_ve = 0;
-    uint32_t n_hdr, hdr_err = 0;
-    if (force_scalar || is_ws(ldb(m + h0)) || is_ws(ldb(m + T - 1))) {    // strip() would move the block's ends
-        WellKnown w2 = wk; uint32_t n2 = 0;
-        hdr_err = headers_scalar(m, h0, T + 4, dst, stride, cap, &n2, &w2);
-        wk = w2; n_hdr = n2;
-    } else {
-        // turn the staged events into records, in place: strip the value, note the two keys that matter
-        n_hdr = min(s.n_ev, s.first_bad);
-        if (s.first_bad < s.n_ev) hdr_err = s.bad_cnt ? (uint32_t)SHL_E_HDR_MULTI_SEP : (uint32_t)SHL_E_HDR_NO_SEP;
-        const uint32_t n_conv = min(n_hdr, cap);
-        int ls = h0;
-        for (uint32_t k = 0; k < n_conv; k++) {
-            const shl_hdr_span ev = dst[(size_t)k * stride];
-            const int sep = ev.key_off, cr = ev.val_off;
-            int vs = sep + 2, ve = cr;
-            const uint32_t c0 = vs < ve ? ldb(m + vs) : 'x', c1 = ve > vs ? ldb(m + ve - 1) : 'x';
-            if (is_ws(c0) || is_ws(c1)) {
-                while (vs < ve && is_ws(ldb(m + vs))) vs++;
-                while (ve > vs && is_ws(ldb(m + ve - 1))) ve--;
+    int p = -lead;                                 // message position of byte 0 of the current vector
+    int idx = -1, T = -1, last_cr = -4;
+    uint32_t n_c = 0, n_s = 0, prev_cr = 0, prev_co = 0;
+    bool ovf = false;
+    uint4 v = __ldg(vp), v1 = __ldg(vp + 1);
+    for (int i = 0; i < 2 * nsec; i++, p += 16) {
+        uint4 nx = make_uint4(0u, 0u, 0u, 0u);
+        if (i + 2 < 2 * nsec) nx = __ldg(vp + i + 2);                // two vectors (one sector) ahead
+        if (p < L) {
+            const uint32_t cr0 = eqf(v.x, K.cr, K), cr1 = eqf(v.y, K.cr, K), cr2 = eqf(v.z, K.cr, K), cr3 = eqf(v.w, K.cr, K);
+            const uint32_t co0 = eqf(v.x, K.col, K), co1 = eqf(v.y, K.col, K), co2 = eqf(v.z, K.col, K), co3 = eqf(v.w, K.col, K);
+            uint32_t c16 = mask16(eqf_and(v.x, K.lf, __funnelshift_l(prev_cr, cr0, 8), K), eqf_and(v.y, K.lf, __funnelshift_l(cr0, cr1, 8), K),
+                                  eqf_and(v.z, K.lf, __funnelshift_l(cr1, cr2, 8), K), eqf_and(v.w, K.lf, __funnelshift_l(cr2, cr3, 8), K));
+            uint32_t s16 = mask16(eqf_and(v.x, K.sp, __funnelshift_l(prev_co, co0, 8), K), eqf_and(v.y, K.sp, __funnelshift_l(co0, co1, 8), K),
+                                  eqf_and(v.z, K.sp, __funnelshift_l(co1, co2, 8), K), eqf_and(v.w, K.sp, __funnelshift_l(co2, co3, 8), K));
+            prev_cr = cr3; prev_co = co3;
+            if (p < 1 || p + 16 > L) { const uint32_t vm = rng16(1 - p, L - p); c16 &= vm; s16 &= vm; }   // pair ends live in [1, L)
+            while (s16) {                          // ": " positions (of the ':')
+                const int k = __ffs(s16) - 1;
+                s16 &= s16 - 1u;
+                if (n_s >= (uint32_t)kSepCap) { ovf = true; break; }
+                sp[n_s * 32] = (uint16_t)(p + k - 1);
+                n_s++;
             }
-            const int klen = sep - ls;
-            shl_hdr_span rec;
-            rec.key_off = (uint16_t)ls; rec.key_len = (uint16_t)klen;
-            rec.val_off = (uint16_t)vs; rec.val_len = (uint16_t)(ve - vs);
-            dst[(size_t)k * stride] = rec;
-            if (klen == 14) { if (span_eq_lower(m, ls, sep, "content-length")) { if (!wk.n_cl) { wk.cl_vs = vs; wk.cl_ve = ve; } wk.n_cl++; } }
-            else if (klen == 17) { if (span_eq_lower(m, ls, sep, "transfer-encoding")) { if (!wk.n_te) { wk.te_vs = vs; wk.te_ve = ve; } wk.n_te++; } }
-            ls = cr + 2;
+            while (c16) {                          // CRLF positions (of the CR)
+                const int k = __ffs(c16) - 1;
+                c16 &= c16 - 1u;
+                const int pos = p + k - 1;
+                if (pos == last_cr + 2 && n_c >= 2u) { T = last_cr; break; }     // empty line after the first line: CRLFCRLF
+                if (n_c >= (uint32_t)kCrCap) { ovf = true; break; }
+                idx = n_c ? idx : pos;
+                cr[n_c * 32] = (uint16_t)pos;
+                n_c++; last_cr = pos;
+            }
+            if (T >= 0 || ovf) break;
         }
+        v = v1; v1 = nx;
     }
-    r.n_headers = n_hdr;
-    if (hdr_err) { r.status |= hdr_err; return; }
-    if (n_hdr > cap) return;                       // not all lines were staged: the caller re-runs this message
-    finalize_headers(m, L, T + 4, get_or_head, wk, r.status, r.content_len);
+    o.idx = idx; o.T = T; o.n_c = n_c; o.n_s = n_s; o.ovf = ovf;
+}
+
+// ----------------------------------------------------------------------------------- epilogue helpers
+// Canonical request line  METHOD SP URL SP "HTTP/1.x" CRLF  (no other space, no trailing blank):
+// fills the first-line fields and returns true; anything else goes to first_line_scalar.
+__device__ __forceinline__ bool first_line_fast(const uint8_t* m, const int idx, const SwarK& K, Msg& r, bool& get_or_head) {
+    const int sp2 = idx - 9;
+    if (sp2 < 1) return false;
+    const uint32_t w0 = ld32u(m + sp2 + 1), w1 = ld32u(m + sp2 + 5);
+    if (ldb(m + sp2) != ' ' || w0 != 0x50545448u || (w1 != 0x312E312Fu && w1 != 0x302E312Fu)) return false;
+    // exactly one space in [0, sp2): SWAR over the aligned vectors that cover it
+    const int lead = (int)(reinterpret_cast<uintptr_t>(m) & 15);
+    const uint4* vp = reinterpret_cast<const uint4*>(m - lead);
+    const int nv = (lead + sp2 + 15) >> 4;
+    int nsp = 0, sp1 = -1, p = -lead;
+    for (int i = 0; i < nv; i++, p += 16) {
+        const uint4 v = __ldg(vp + i);
+        uint32_t z = mask16(eqf(v.x, K.sp, K), eqf(v.y, K.sp, K), eqf(v.z, K.sp, K), eqf(v.w, K.sp, K));
+        if (p < 0 || p + 16 > sp2) z &= rng16(-p, sp2 - p);
+        if (z && sp1 < 0) sp1 = p + __ffs(z) - 1;
+        nsp += __popc(z);
+    }
+    if (nsp != 1) return false;
+    const uint32_t f4 = ld32u(m);
+    if ((f4 & 0xffffu) == 0x5448u && sp1 >= 2) return false;            // a.startswith('HT'): a response
+    r.sp1 = (uint32_t)sp1; r.sp2 = (uint32_t)sp2; r.fl_end = (uint32_t)idx; r.slash = (uint32_t)(sp2 + 5);
+    r.status = (r.status & ~SHL_F_VERSION_MASK) | ((w1 >> 24) == '1' ? 1u << SHL_F_VERSION_SHIFT : 0u) | SHL_F_FIRST_LINE_DONE;
+    get_or_head = (sp1 == 3 && (f4 & 0xffffffu) == 0x544547u) || (sp1 == 4 && f4 == 0x44414548u);
+    return true;
+}
+
+__device__ __noinline__ int find_crlf_scalar(const uint8_t* m, int from, int L) {
+    for (int i = from; i + 1 < L; i++) if (ldb(m + i) == '\r' && ldb(m + i + 1) == '\n') return i;
+    return -1;
+}
+__device__ __noinline__ int find_term_scalar(const uint8_t* m, int from, int L) {
+    for (int i = from; i + 3 < L; i++)
+        if (ldb(m + i) == '\r' && ldb(m + i + 1) == '\n' && ldb(m + i + 2) == '\r' && ldb(m + i + 3) == '\n') return i;
+    return -1;
 }
 
 // ----------------------------------------------------------------------------------- kernel
 template <bool kPlace>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, 8) k_route(const RouteArgs a) {
-    __shared__ shl_hdr_span stage[kWarpsPerBlock][kLaneCap * 32];
+    __shared__ uint16_t s_cr[kWarpsPerBlock][kCrCap * 32];
+    __shared__ uint16_t s_sp[kWarpsPerBlock][kSepCap * 32];
     __shared__ uint32_t s_codes[64];
     extern __shared__ uint32_t s_hist[];                       // kPlace: n_hosts bins (when they fit)
 
@@ -364,13 +300,71 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 8) k_route(const RouteArg
         const uint64_t my_off = have ? a.off[mine] : 0ull;
         const int L = have ? (int)min(a.len[mine], 0x7fffffc0u) : 0;
         const uint8_t* m = a.arena + my_off;
-        shl_hdr_span* my_stage = &stage[warp][lane];
-        Msg r;
-        scan_message(m, L, my_stage, 32, (uint32_t)kLaneCap, K, a.force_scalar != 0, r);
-        const bool ovf = r.n_headers > (uint32_t)kLaneCap;
+        uint16_t* cr = &s_cr[warp][lane];
+        uint16_t* sp = &s_sp[warp][lane];
+        const bool force = a.force_scalar != 0;
 
-        // ---- one atomic allocates the group's header records; lanes copy their own out
-        uint32_t nh = have ? r.n_headers : 0u;
+        // ---- scan (lanes diverge on their own events; nothing heavy happens in here)
+        LaneScan sc; sc.idx = sc.T = -1; sc.n_c = sc.n_s = 0; sc.ovf = false;
+        if (L > 0) scan_lists(m, L, cr, sp, K, sc);
+
+        // ---- first line, header block bounds, line count
+        Msg r;
+        r.status = (3u << SHL_F_VERSION_SHIFT) | SHL_F_IS_REQUEST;
+        r.first_line_len = r.headers_len = r.sp1 = r.sp2 = r.fl_end = r.slash = r.n_headers = 0;
+        r.status_code = 0; r.content_len = 0;
+        WellKnown wk; wk.n_te = wk.n_cl = 0; wk.te_vs = wk.te_ve = wk.cl_vs = wk.cl_ve = 0;
+        uint32_t n_hdr = 0, hdr_err = 0;
+        int h0 = 0, T = -1;
+        bool get_or_head = false, slow = false, hdr_state = false;   // hdr_state: the header block will be tokenised
+        if (L == 0) r.status |= SHL_S_EMPTY;
+        else {
+            int idx = sc.idx;
+            if (sc.ovf && sc.n_c == 0u) idx = find_crlf_scalar(m, 0, L);
+            if (idx < 0) r.status |= SHL_S_INCOMPLETE_LINE;
+            else {
+                r.first_line_len = (uint32_t)(idx + 2);
+                uint32_t fl_code = 0;
+                if (force || !first_line_fast(m, idx, K, r, get_or_head)) {
+                    Msg t = r; bool goh = false;   // the cold path may keep its copy in local memory
+                    fl_code = first_line_scalar(m, idx, t, goh);
+                    r = t; get_or_head = goh;
+                }
+                if (fl_code) r.status |= fl_code;
+                else {
+                    h0 = idx + 2;
+                    T = sc.ovf ? find_term_scalar(m, h0, L) : sc.T;
+                    if (T < 0) r.status |= SHL_S_INCOMPLETE_HEADERS;
+                    else if (T + 4 > 65536) r.status |= SHL_E_LIB_HDR_TOO_LARGE;
+                    else {
+                        r.headers_len = (uint32_t)(T + 4 - h0);
+                        hdr_state = true;
+                        slow = sc.ovf || force || is_ws(ldb(m + h0)) || is_ws(ldb(m + T - 1));   // strip() would move the block's ends
+                        if (slow) {                // count (and classify) now, emit after the allocation
+                            WellKnown w2 = wk; uint32_t n2 = 0;
+                            hdr_err = headers_scalar(m, h0, T + 4, nullptr, 1, 0u, &n2, &w2);
+                            wk = w2; n_hdr = n2;
+                        } else {
+                            // sorted merge: line k = (cr[k-1] + 2, cr[k]) must hold exactly one ": ";
+                            // its position is compacted into sp[k-1]
+                            uint32_t j = 0;
+                            while (j < sc.n_s && (int)sp[j * 32] < h0) j++;
+                            for (uint32_t k = 1; k < sc.n_c; k++) {
+                                const uint32_t end = cr[k * 32];
+                                uint32_t cnt = 0, fs = 0;
+                                while (j < sc.n_s && sp[j * 32] < end) { if (!cnt) fs = sp[j * 32]; cnt++; j++; }
+                                if (cnt != 1u) { hdr_err = cnt ? (uint32_t)SHL_E_HDR_MULTI_SEP : (uint32_t)SHL_E_HDR_NO_SEP; break; }
+                                sp[(k - 1) * 32] = (uint16_t)fs;
+                                n_hdr++;
+                            }
+                        }
+                    }
+                }
+            }
+        }
+
+        // ---- one atomic allocates the group's header records
+        uint32_t nh = have ? n_hdr : 0u;
         uint32_t inc = nh;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(SHL_FULL, inc, d); if (lane >= d) inc += t; }
@@ -379,19 +373,40 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 8) k_route(const RouteArg
         if (lane == 0 && total) base = atomicAdd(reinterpret_cast<unsigned long long*>(a.out.hdr_used), (unsigned long long)total);
         base = __shfl_sync(SHL_FULL, base, 0);
         const unsigned long long my_base = base + (inc - nh);
-        if (my_base + nh > a.out.hdr_cap) {                    // record arena full: library limit
-            r.status = (r.status & ~0xffu & ~SHL_F_MESSAGE_COMPLETE) | SHL_E_LIB_RECORDS_FULL;
-            nh = 0; r.n_headers = 0;
+        const bool fits = my_base + nh <= a.out.hdr_cap;
+        if (!fits) {                                           // record arena full: library limit
+            r.status = (r.status & ~0xffu) | SHL_E_LIB_RECORDS_FULL;
+            nh = 0; hdr_state = false;
         }
-        if (!ovf) {
-            uint2* g = reinterpret_cast<uint2*>(a.out.hdr + my_base);
-            const uint2* sgl = reinterpret_cast<const uint2*>(my_stage);
-#pragma unroll 4
-            for (uint32_t k = 0; k < nh; k++) g[k] = sgl[k * 32];
-        } else if (nh) {                                       // more lines than staging slots: redo, straight to global
-            Msg r2;
-            scan_message(m, L, a.out.hdr + my_base, 1, nh, K, a.force_scalar != 0, r2);
-            r = r2;
+
+        // ---- records: strip the value (HttpParser.py:329), note the two keys that matter
+        if (hdr_state) {
+            shl_hdr_span* out = a.out.hdr + my_base;
+            if (slow) {
+                WellKnown w2; uint32_t n2 = 0;
+                w2.n_te = w2.n_cl = 0; w2.te_vs = w2.te_ve = w2.cl_vs = w2.cl_ve = 0;
+                headers_scalar(m, h0, T + 4, out, 1, nh, &n2, &w2);
+            } else {
+                int ls = h0;
+                for (uint32_t k = 0; k < nh; k++) {
+                    const int sep = sp[k * 32], end = cr[(k + 1) * 32];
+                    int vs = sep + 2, ve = end;
+                    const uint32_t c0 = vs < ve ? ldb(m + vs) : 'x', c1 = ve > vs ? ldb(m + ve - 1) : 'x';
+                    if (is_ws(c0) || is_ws(c1)) {
+                        while (vs < ve && is_ws(ldb(m + vs))) vs++;
+                        while (ve > vs && is_ws(ldb(m + ve - 1))) ve--;
+                    }
+                    const int klen = sep - ls;
+                    const uint32_t lo = (uint32_t)ls | ((uint32_t)klen << 16), hi = (uint32_t)vs | ((uint32_t)(ve - vs) << 16);
+                    *reinterpret_cast<uint2*>(out + k) = make_uint2(lo, hi);
+                    if (klen == 14) { if (span_eq_lower(m, ls, sep, "content-length")) { if (!wk.n_cl) { wk.cl_vs = vs; wk.cl_ve = ve; } wk.n_cl++; } }
+                    else if (klen == 17) { if (span_eq_lower(m, ls, sep, "transfer-encoding")) { if (!wk.n_te) { wk.te_vs = vs; wk.te_ve = ve; } wk.n_te++; } }
+                    ls = end + 2;
+                }
+            }
+            r.n_headers = nh;
+            if (hdr_err) r.status |= hdr_err;
+            else finalize_headers(m, L, T + 4, get_or_head, wk, r.status, r.content_len);
         }
 
         // ---- per-message fixed fields: lane j == message j, so these are coalesced SoA stores
