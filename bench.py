@@ -340,6 +340,15 @@ def run_ours(args):
         eng.route(ar, pout=pout, qout=qout, sync=True)
 
     e_ms, e_clocks, _ = timed(step_e2e, args.steps, max(args.warmup, 1))
+    # PCIe roofline of this box, measured in the same run: one pinned copy each way of the step's bytes
+    eng.sync()
+    pcie = {}
+    for name, fn in (('h2d', lambda: eng.h2d(d_arena, ar.data, nbytes)), ('d2h', lambda: eng.d2h(ar.data, d_arena, nbytes))):
+        best = 1e9
+        for _ in range(3):
+            eng.event(4); fn(); eng.event(5); eng.sync()
+            best = min(best, eng.elapsed_ms(4, 5))
+        pcie[name + '_gb_s'] = nbytes / (best / 1e3) / 1e9
     assert int(qout.hist.sum()) == n and (pout.code() == 0).all()
     n_hdr = int(total_hdrs[0])
     h2d = nbytes + n * 12
@@ -364,6 +373,8 @@ def run_ours(args):
         'e2e': {'value': e2e, 'unit': 'requests/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
                 'header_gb_s': nbytes * world * args.steps / (e_ms / 1e3) / 1e9,
                 'pcie_gb_s_h2d': h2d * args.steps / (e_ms / 1e3) / 1e9, 'ms_per_step': e_ms / args.steps,
+                'pcie_probe': pcie, 'frac_of_pcie_h2d_roofline': (h2d * args.steps / (e_ms / 1e3) / 1e9) / pcie['h2d_gb_s'],
+                'note': 'chunked over 4 streams: H2D, kernel and D2H of different chunks overlap; bound by the H2D link',
                 'clocks': e_clocks},
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
                      'traffic': ncu_traffic(), 'kernel': 'shl::k_route<true>', 'kernel_ms': k_ms,

@@ -28,6 +28,7 @@ class Arena(object):
     def __init__(self, data, off, length):
         self.data, self.off, self.len = data, off, length
         self.n = int(len(off))
+        self._nbytes = None
 
     @classmethod
     def pack(cls, messages, alloc=_np_alloc, align=1):
@@ -53,7 +54,12 @@ class Arena(object):
 
     @property
     def nbytes(self):
-        return int(self.off[-1] + self.len[-1]) if self.n else 0
+        """One past the last message byte (messages need not be stored in index order)."""
+        if not self.n:
+            return 0
+        if self._nbytes is None:
+            self._nbytes = int((self.off.astype(np.uint64) + self.len.astype(np.uint64)).max())
+        return self._nbytes
 
     def message(self, i):
         o = int(self.off[i])

@@ -45,6 +45,13 @@ struct shl_ctx {
     uint64_t* d_hist = nullptr; uint32_t hist_cap = 0;
     int force_scalar = 0;
     uint64_t launches = 0;
+    // pipelined host-buffer path: chunks round-robin over these streams so H2D, kernel and D2H overlap
+    static constexpr int kPipe = 4, kMaxChunks = 16;
+    cudaStream_t pipe[kPipe]{};
+    cudaEvent_t ev_fork = nullptr, ev_join[kPipe]{}, ev_chunk[kMaxChunks]{};
+    uint64_t* d_chunk_used = nullptr;     // [kMaxChunks]
+    uint64_t* h_chunk_used = nullptr;     // pinned mirror
+    int pipeline = 1;                     // SHL_PIPELINE=0 disables the chunked path
     std::string err;
 };
 
@@ -167,6 +174,13 @@ int shl_ctx_create(int device, uint64_t max_msgs, uint64_t max_bytes, uint64_t m
     CU(dalloc(&ctx->d_ch_len, n)); CU(dalloc(&ctx->d_ch_size, n)); CU(dalloc(&ctx->d_ch_ok, n));
     CU(cudaFuncSetAttribute(shl::k_route<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
     CU(cudaFuncSetAttribute(shl::k_route<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
+    for (auto& st : ctx->pipe) CU(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+    for (auto& e : ctx->ev_join) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (auto& e : ctx->ev_chunk) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    CU(dalloc(&ctx->d_chunk_used, shl_ctx::kMaxChunks));
+    CU(cudaHostAlloc(reinterpret_cast<void**>(&ctx->h_chunk_used), shl_ctx::kMaxChunks * sizeof(uint64_t), cudaHostAllocDefault));
+    { const char* pl = getenv("SHL_PIPELINE"); if (pl && pl[0] == '0') ctx->pipeline = 0; }
     const char* fs = getenv("SHL_FORCE_SCALAR");
     ctx->force_scalar = (fs && fs[0] == '1') ? 1 : 0;
     *out = ctx;
@@ -186,6 +200,11 @@ void shl_ctx_destroy(shl_ctx* ctx) {
     cudaFree(ctx->d_counters); cudaFreeHost(ctx->h_counters);
     cudaFree(ctx->d_ring_values); cudaFree(ctx->d_ring_nodes); cudaFree(ctx->d_hist);
     for (auto& e : ctx->ev) cudaEventDestroy(e);
+    for (auto& st : ctx->pipe) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
+    cudaEventDestroy(ctx->ev_fork);
+    for (auto& e : ctx->ev_join) cudaEventDestroy(e);
+    for (auto& e : ctx->ev_chunk) cudaEventDestroy(e);
+    cudaFree(ctx->d_chunk_used); cudaFreeHost(ctx->h_chunk_used);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -315,7 +334,8 @@ static int check_arena(shl_ctx* ctx, const void* arena) {
 }
 
 static int launch_route(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_off, const uint32_t* d_len, uint64_t n,
-                        const shl_parse_out* d_out, const shl_place_out* d_q) {
+                        const shl_parse_out* d_out, const shl_place_out* d_q, cudaStream_t stream = nullptr, uint32_t bias = 0) {
+    if (!stream && ctx) stream = ctx->stream;
     if (!ctx || !d_arena || !d_off || !d_len || !d_out) return fail(ctx, SHL_ERR_ARG, "null pointer");
     if (int rc = check_arena(ctx, d_arena)) return rc;
     if (d_q && !ctx->d_ring_values) return fail(ctx, SHL_ERR_NO_RING, "shl_ring_build() has not been called");
@@ -324,15 +344,16 @@ static int launch_route(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_
     a.arena = d_arena; a.off = d_off; a.len = d_len; a.n = n; a.out = *d_out;
     a.code_hist = ctx->d_counters + 2; a.force_scalar = ctx->force_scalar;
     a.k = shl::swar_host_consts();
+    a.hdr_base_bias = bias;
     const uint64_t groups = (n + shl::kGroup - 1) / shl::kGroup;
     const unsigned blocks = (unsigned)((groups + shl::kWarpsPerBlock - 1) / shl::kWarpsPerBlock);
     if (d_q) {
         a.ring_values = ctx->d_ring_values; a.ring_nodes = ctx->d_ring_nodes;
         a.n_points = ctx->n_points; a.n_hosts = ctx->n_hosts; a.place = *d_q;
         const size_t sh = (d_q->hist && ctx->n_hosts <= 4096u) ? ctx->n_hosts * 4 : 0;
-        shl::k_route<true><<<blocks, shl::kWarpsPerBlock * 32, sh, ctx->stream>>>(a);
+        shl::k_route<true><<<blocks, shl::kWarpsPerBlock * 32, sh, stream>>>(a);
     } else {
-        shl::k_route<false><<<blocks, shl::kWarpsPerBlock * 32, 0, ctx->stream>>>(a);
+        shl::k_route<false><<<blocks, shl::kWarpsPerBlock * 32, 0, stream>>>(a);
     }
     ctx->launches++;
     CU(cudaGetLastError());
@@ -423,9 +444,100 @@ static int place_out_d2h(shl_ctx* ctx, const shl_place_out* out, uint64_t n) {
     return SHL_OK;
 }
 
+// ---- chunked, multi-stream version of parse/route for large batches -----------------------------
+// The batch is cut into message ranges; chunk c runs H2D(arena slice, index slice) -> kernel ->
+// D2H(result slices) on stream c % kPipe, so the copy engines of both directions and the SMs are
+// busy at the same time (PCIe is full duplex; one stream would serialise the three stages).
+// Each chunk owns a slice of the record arena and its own allocation counter; hdr_base values are
+// biased so they index the caller's arena directly.  Returns 1 when the batch is not chunkable
+// (offsets not locally dense) so the caller falls back to the single-stream path.
+static int route_pipelined(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, const uint64_t* off, const uint32_t* len,
+                           uint64_t n, const shl_parse_out* pout, const shl_place_out* qout) {
+    constexpr int kPipe = shl_ctx::kPipe, kMaxChunks = shl_ctx::kMaxChunks;
+    if (!ctx->pipeline || !arena || n < 65536) return 1;
+    const int nch = (int)std::min<uint64_t>(kMaxChunks, std::max<uint64_t>(2, n / 65536));
+    const uint64_t per = ((n + nch - 1) / nch + 31) & ~31ull;
+    // cheap density probe (the exact byte range of a chunk is computed right before it is queued,
+    // so the host scan of the index overlaps the copies of the previous chunks): the arena is
+    // chunkable when sampled offsets are non-decreasing
+    {
+        const uint64_t stride = std::max<uint64_t>(1, n / 2048);
+        uint64_t prev = 0;
+        for (uint64_t i = 0; i < n; i += stride) { if (off[i] < prev) return 1; prev = off[i]; }
+    }
+    const uint64_t host_cap = pout->hdr ? pout->hdr_cap : ctx->dp.hdr_cap;
+    const uint64_t cap_c = std::min<uint64_t>(ctx->dp.hdr_cap, host_cap) / nch;
+    if (cap_c == 0 || cap_c * nch > 0xffffffffull) return 1;
+    CU(cudaMemsetAsync(ctx->d_chunk_used, 0, kMaxChunks * 8, ctx->stream));
+    shl_place_out dq = ctx->dq;
+    if (qout) {
+        dq.hist = qout->hist ? ctx->d_hist : nullptr;
+        if (dq.hist) CU(cudaMemsetAsync(ctx->d_hist, 0, (size_t)ctx->n_hosts * 8, ctx->stream));
+    }
+    CU(cudaEventRecord(ctx->ev_fork, ctx->stream));
+    for (int s = 0; s < kPipe; s++) CU(cudaStreamWaitEvent(ctx->pipe[s], ctx->ev_fork, 0));
+    const shl_parse_out& d = ctx->dp;
+#define D2S(dst, src, cnt, esz) do { if (dst) CU(cudaMemcpyAsync((uint8_t*)(dst) + i0 * (esz), (const uint8_t*)(src) + i0 * (esz), (cnt) * (esz), cudaMemcpyDeviceToHost, st)); } while (0)
+    for (int c = 0; c < nch; c++) {
+        const uint64_t i0 = std::min<uint64_t>(n, c * per), i1 = std::min<uint64_t>(n, i0 + per), m = i1 - i0;
+        if (!m) continue;
+        cudaStream_t st = ctx->pipe[c % kPipe];
+        uint64_t lo = ~0ull, hi = 0;
+        for (uint64_t i = i0; i < i1; i++) { lo = std::min(lo, off[i]); hi = std::max(hi, off[i] + len[i]); }
+        if (hi > arena_bytes) return fail(ctx, SHL_ERR_ARG, "a message lies outside the arena");
+        lo &= ~31ull;
+        CU(cudaMemcpyAsync(ctx->d_arena + lo, arena + lo, hi - lo, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(ctx->d_off + i0, off + i0, m * 8, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(ctx->d_len + i0, len + i0, m * 4, cudaMemcpyHostToDevice, st));
+        shl_parse_out o = d;
+        o.status += i0; o.first_line_len += i0; o.headers_len += i0; o.sp1 += i0; o.sp2 += i0; o.fl_end += i0; o.slash += i0;
+        o.status_code += i0; o.n_headers += i0; o.hdr_base += i0; o.content_len += i0;
+        o.hdr = d.hdr + (uint64_t)c * cap_c; o.hdr_cap = cap_c; o.hdr_used = ctx->d_chunk_used + c;
+        shl_place_out q = dq;
+        if (qout) { q.md5 += 16 * i0; q.hash += i0; q.node += i0; }
+        if (int rc = launch_route(ctx, ctx->d_arena, ctx->d_off + i0, ctx->d_len + i0, m, &o, qout ? &q : nullptr, st,
+                                  (uint32_t)((uint64_t)c * cap_c))) return rc;
+        D2S(pout->status, d.status, m, 4); D2S(pout->first_line_len, d.first_line_len, m, 4); D2S(pout->headers_len, d.headers_len, m, 4);
+        D2S(pout->sp1, d.sp1, m, 4); D2S(pout->sp2, d.sp2, m, 4); D2S(pout->fl_end, d.fl_end, m, 4); D2S(pout->slash, d.slash, m, 4);
+        D2S(pout->status_code, d.status_code, m, 4); D2S(pout->n_headers, d.n_headers, m, 4); D2S(pout->hdr_base, d.hdr_base, m, 4);
+        D2S(pout->content_len, d.content_len, m, 8);
+        if (qout) { D2S(qout->md5, dq.md5, m, 16); D2S(qout->hash, dq.hash, m, 4); D2S(qout->node, dq.node, m, 4); }
+        CU(cudaMemcpyAsync(ctx->h_chunk_used + c, ctx->d_chunk_used + c, 8, cudaMemcpyDeviceToHost, st));
+        CU(cudaEventRecord(ctx->ev_chunk[c], st));
+    }
+#undef D2S
+    // the record count of a chunk is only known once its kernel ran: fetch exactly that many
+    uint64_t used_total = 0; bool overflow = false;
+    for (int c = 0; c < nch; c++) {
+        const uint64_t i0 = std::min<uint64_t>(n, c * per), i1 = std::min<uint64_t>(n, i0 + per);
+        if (i0 == i1) continue;
+        CU(cudaEventSynchronize(ctx->ev_chunk[c]));
+        const uint64_t used = ctx->h_chunk_used[c];
+        used_total += std::min(used, cap_c);
+        if (used > cap_c) overflow = true;
+        const uint64_t copy = std::min(used, cap_c);
+        if (pout->hdr && copy)
+            CU(cudaMemcpyAsync(pout->hdr + (uint64_t)c * cap_c, d.hdr + (uint64_t)c * cap_c, copy * sizeof(shl_hdr_span),
+                               cudaMemcpyDeviceToHost, ctx->pipe[c % kPipe]));
+    }
+    if (pout->hdr_used) *pout->hdr_used = used_total;
+    for (int s = 0; s < kPipe; s++) {
+        CU(cudaEventRecord(ctx->ev_join[s], ctx->pipe[s]));
+        CU(cudaStreamWaitEvent(ctx->stream, ctx->ev_join[s], 0));
+    }
+    if (qout) { shl_place_out only_hist{}; only_hist.hist = qout->hist; if (int rc = place_out_d2h(ctx, &only_hist, 0)) return rc; }
+    if (overflow) return fail(ctx, SHL_ERR_CAPACITY, "header record arena overflowed: raise max_records / hdr_cap");
+    return SHL_OK;
+}
+
 int shl_parse_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, const uint64_t* off, const uint32_t* len,
                     uint64_t n, const shl_parse_out* out) {
     if (!out) return fail(ctx, SHL_ERR_ARG, "out is null");
+    if (ctx && off && len && n <= ctx->max_msgs && arena_bytes <= ctx->max_bytes) {
+        CU(cudaSetDevice(ctx->device));
+        const int rc = route_pipelined(ctx, arena, arena_bytes, off, len, n, out, nullptr);
+        if (rc <= 0) return rc;
+    }
     if (int rc = stage_in(ctx, arena, arena_bytes, off, len, n, ctx->d_off, ctx->d_len)) return rc;
     CU(cudaMemsetAsync(ctx->d_counters, 0, 8, ctx->stream));
     if (int rc = shl_parse_dev(ctx, ctx->d_arena, ctx->d_off, ctx->d_len, n, &ctx->dp)) return rc;
@@ -436,6 +548,11 @@ int shl_route_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, co
                     uint64_t n, const shl_parse_out* pout, const shl_place_out* qout) {
     if (!pout || !qout) return fail(ctx, SHL_ERR_ARG, "out is null");
     if (ctx && !ctx->d_ring_values) return fail(ctx, SHL_ERR_NO_RING, "shl_ring_build() has not been called");
+    if (ctx && off && len && n <= ctx->max_msgs && arena_bytes <= ctx->max_bytes) {
+        CU(cudaSetDevice(ctx->device));
+        const int rc = route_pipelined(ctx, arena, arena_bytes, off, len, n, pout, qout);
+        if (rc <= 0) return rc;
+    }
     if (int rc = stage_in(ctx, arena, arena_bytes, off, len, n, ctx->d_off, ctx->d_len)) return rc;
     CU(cudaMemsetAsync(ctx->d_counters, 0, 8, ctx->stream));
     shl_place_out dq = ctx->dq;

@@ -77,6 +77,7 @@ struct RouteArgs {
     shl_parse_out out; uint64_t* code_hist;
     int force_scalar;                 // test hook: take the scalar path for every message
     SwarK k;                          // SWAR byte constants, as run-time values (see SwarK)
+    uint32_t hdr_base_bias;           // added to the stored hdr_base (out.hdr may be a slice of a larger arena)
     // fused placement (route); ring_values == nullptr -> parse only
     const uint32_t* ring_values; const uint32_t* ring_nodes; uint32_t n_points, n_hosts;
     shl_place_out place;
@@ -418,7 +419,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 8) k_route(const RouteArg
             a.out.fl_end[mine] = r.fl_end; a.out.slash[mine] = r.slash;
             a.out.status_code[mine] = r.status_code;
             a.out.n_headers[mine] = r.n_headers;
-            a.out.hdr_base[mine] = (uint32_t)my_base;
+            a.out.hdr_base[mine] = (uint32_t)my_base + a.hdr_base_bias;
             a.out.content_len[mine] = r.content_len;
             atomicAdd(&s_codes[r.status & 63u], 1u);
         }

@@ -165,6 +165,24 @@ def test_c2_corpus_parse_matches_oracle(eng):
     assert_parse_equal(ar, g2, o, 'c2 60k scalar path')
 
 
+def test_large_batches_take_the_pipelined_path_and_still_match(eng):
+    """>= 64 K messages go through the chunked multi-stream path (H2D / kernel / D2H overlapped,
+    one record sub-arena per chunk); a batch whose offsets are not locally dense falls back to the
+    single-stream path.  Both must equal the oracle."""
+    n = 150000
+    ar = eng.corpus_host(99, 5000, n, 0)
+    o = O.orc_parse(ar, hdr_cap=n * 24)
+    g = eng.parse(ar, hdr_cap=n * 24)
+    assert_parse_equal(ar, g, o, 'pipelined parse 150k')
+    # same messages, index order shuffled: every chunk spans the whole arena -> fallback path
+    perm = np.random.default_rng(8).permutation(n)
+    a_off, a_len = eng.pinned(n, np.uint64), eng.pinned(n, np.uint32)
+    a_off[:] = ar.off[perm]
+    a_len[:] = ar.len[perm]
+    ar2 = Arena(ar.data, a_off, a_len)
+    assert_parse_equal(ar2, eng.parse(ar2, hdr_cap=n * 24), O.orc_parse(ar2, hdr_cap=n * 24), 'shuffled 150k (fallback)')
+
+
 def test_c2_corpus_every_alignment_and_tail(eng):
     """Messages at all 16 alignments, and truncated at every length around the chunk edges."""
     rng = np.random.default_rng(2)
