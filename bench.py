@@ -262,7 +262,8 @@ def run_ours(args):
     if world > 1:
         stats = torch.zeros(n_stat, dtype=torch.int64, device='cuda:%d' % local)   # [hist | code counts]
         d_stats = stats.data_ptr()
-        ext = torch.cuda.ExternalStream(lib.shl_stream(ctx), device='cuda:%d' % local)
+        from shellac_b200 import dist as D
+        ext = D.external_stream(eng, local)
     else:
         d_stats = eng.dev_alloc(n_stat * 8)
     qs.hist = d_stats
@@ -277,7 +278,7 @@ def run_ours(args):
         lib.shl_memcpy_d2d(ctx, d_stats + len(HOSTS) * 8, d_codes, N.N_CODES * 8)
         if world > 1:
             with torch.cuda.stream(ext):
-                dist.all_reduce(stats)
+                D.allreduce_stats(stats)
 
     def barrier():
         eng.sync()
