@@ -382,14 +382,28 @@ def run_ours(args):
                      'algorithmic_bytes_per_launch': alg_bytes, 'bytes_per_request': alg_bytes / n,
                      'peak_source': peak_src, 'frac_of_nominal_8TBs': achieved / 8000.0},
     }
-    if rank == 0:
-        if world == 1 and not args.no_cpu:
-            line['cpu_baseline'] = cpu_baseline_single()
-        print(json.dumps(line), flush=True)
+    if rank == 0 and world == 1 and not args.no_cpu:
+        line['cpu_baseline'] = cpu_baseline_single()
     eng.close()
     if world > 1:
         dist.destroy_process_group()
-    return 0
+    return line if rank == 0 else None
+
+
+class StdoutToStderr(object):
+    """Everything a library prints on fd 1 while we work (NCCL's version banner, for one) goes to
+    stderr, so that stdout carries exactly ONE line: the JSON result."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        os.dup2(2, 1)
+        return self
+
+    def __exit__(self, *exc):
+        sys.stdout.flush()
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
 
 
 def main():
@@ -404,7 +418,11 @@ def main():
     args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
     if args.impl == 'reference':
         return run_reference(args)
-    return run_ours(args)
+    with StdoutToStderr():
+        line = run_ours(args)
+    if line is not None:
+        print(json.dumps(line), flush=True)
+    return 0
 
 
 if __name__ == '__main__':

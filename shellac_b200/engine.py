@@ -185,6 +185,34 @@ class Engine(object):
         _check(self.lib, self.ctx, self.lib.shl_corpus_fill_host(seed, first, n, kind, off.ctypes.data, data.ctypes.data), 'corpus_fill')
         return Arena(data, off[:n], ln[:n])
 
+    # -- device-resident batches (arenas that already live in HBM; kernel-only timing) ---------
+    def corpus_dev(self, seed, first, n, kind=0):
+        """Generate messages [first, first+n) directly in HBM.  Returns a DeviceBatch."""
+        d_len = self.dev_alloc(n * 4)
+        _check(self.lib, self.ctx, self.lib.shl_corpus_lengths_dev(self.ctx, seed, first, n, kind, d_len), 'corpus_lengths_dev')
+        ln = np.zeros(n, np.uint32)
+        self.d2h(ln, d_len)
+        self.sync()
+        off = np.zeros(n, np.uint64)
+        if n > 1:
+            np.cumsum(ln[:n - 1], dtype=np.uint64, out=off[1:n])
+        total = int(off[n - 1] + ln[n - 1]) if n else 0
+        d_off, d_arena = self.dev_alloc(n * 8), self.dev_alloc(total + 64)
+        self.h2d(d_off, off)
+        self.memset(d_arena + total, 0, 64)
+        _check(self.lib, self.ctx, self.lib.shl_corpus_fill_dev(self.ctx, seed, first, n, kind, d_off, d_arena), 'corpus_fill_dev')
+        self.sync()
+        return DeviceBatch(self, d_arena, d_off, d_len, n, total, off, ln)
+
+    def upload(self, arena):
+        """Copy a host Arena into HBM.  Returns a DeviceBatch."""
+        n, total = arena.n, arena.nbytes
+        d_arena, d_off, d_len = self.dev_alloc(total + 64), self.dev_alloc(n * 8), self.dev_alloc(n * 4)
+        self.memset(d_arena + total, 0, 64)
+        self.h2d(d_arena, arena.data, total); self.h2d(d_off, arena.off); self.h2d(d_len, arena.len)
+        self.sync()
+        return DeviceBatch(self, d_arena, d_off, d_len, n, total, np.array(arena.off), np.array(arena.len))
+
     def close(self):
         if getattr(self, 'ctx', None):
             self.lib.shl_ctx_destroy(self.ctx)
@@ -198,3 +226,69 @@ class Engine(object):
             self.close()
         except Exception:   # noqa: BLE001 - interpreter shutdown
             pass
+
+
+class DeviceBatch(object):
+    """An arena + index resident in HBM, with device-side result arrays on demand."""
+
+    def __init__(self, eng, d_arena, d_off, d_len, n, nbytes, off, ln):
+        self.eng, self.d_arena, self.d_off, self.d_len = eng, d_arena, d_off, d_len
+        self.n, self.nbytes, self.off, self.len = n, nbytes, off, ln
+        self._bufs = [d_arena, d_off, d_len]
+        self.p = self.q = None
+
+    def _alloc(self, nbytes):
+        p = self.eng.dev_alloc(nbytes)
+        self._bufs.append(p)
+        return p
+
+    def parse_struct(self, hdr_cap=0):
+        if self.p is None:
+            self.hdr_cap = int(hdr_cap) if hdr_cap else self.n * 24
+            self.p = N.ParseOutStruct()
+            self.p_fields = {}
+            for name, dt in N.PARSE_FIELDS:
+                self.p_fields[name] = self._alloc(self.n * np.dtype(dt).itemsize)
+                setattr(self.p, name, self.p_fields[name])
+            self.d_hdr, self.d_used = self._alloc(self.hdr_cap * 8), self._alloc(8)
+            self.p.hdr, self.p.hdr_cap, self.p.hdr_used = self.d_hdr, self.hdr_cap, self.d_used
+        return self.p
+
+    def place_struct(self, n_hosts, md5=True):
+        if self.q is None:
+            self.q = N.PlaceOutStruct()
+            self.d_md5 = self._alloc(16 * self.n) if md5 else None
+            self.d_hash, self.d_node = self._alloc(4 * self.n), self._alloc(4 * self.n)
+            self.d_hist = self._alloc(8 * max(n_hosts, 1))
+            self.n_hosts = n_hosts
+            self.q.md5, self.q.hash, self.q.node, self.q.hist = self.d_md5, self.d_hash, self.d_node, self.d_hist
+            self.eng.memset(self.d_hist, 0, 8 * max(n_hosts, 1))
+        return self.q
+
+    def route(self, n_hosts):
+        """shl_route_dev on the resident batch (asynchronous)."""
+        e = self.eng
+        ps, qs = self.parse_struct(), self.place_struct(n_hosts)
+        e.memset(self.d_used, 0, 8)
+        _check(e.lib, e.ctx, e.lib.shl_route_dev(e.ctx, self.d_arena, self.d_off, self.d_len, self.n, C.byref(ps), C.byref(qs)), 'shl_route_dev')
+
+    def place(self, n_hosts, d_key_off=None, d_key_len=None, md5=False):
+        e = self.eng
+        qs = self.place_struct(n_hosts, md5=md5)
+        _check(e.lib, e.ctx, e.lib.shl_place_dev(e.ctx, self.d_arena, d_key_off or self.d_off, d_key_len or self.d_len, self.n, C.byref(qs)), 'shl_place_dev')
+
+    def fetch(self, dptr, dtype, count):
+        a = np.zeros(count, dtype)
+        self.eng.d2h(a, dptr)
+        self.eng.sync()
+        return a
+
+    def field(self, name):
+        dt = dict(N.PARSE_FIELDS)[name]
+        return self.fetch(self.p_fields[name], dt, self.n)
+
+    def free(self):
+        self.eng.sync()
+        for p in self._bufs:
+            self.eng.dev_free(p)
+        self._bufs = []

@@ -372,3 +372,86 @@ def test_c2_full_size_properties(eng):
     assert (qg.node[:n] == oq.node[:n]).all() and (qg.hash[:n] == oq.hash[:n]).all()
     assert (qg.md5[:16 * n] == oq.md5[:16 * n]).all()
     assert qg.hist.tolist() == oq.hist.tolist()
+
+
+# ------------------------------------------------------------------------------- configs 4 and 5
+def _host_corpus(lib, seed, first, n, kind):
+    ln = np.zeros(n, np.uint32)
+    lib.shl_corpus_lengths_host(seed, first, n, kind, ln.ctypes.data)
+    off = np.zeros(n, np.uint64)
+    np.cumsum(ln[:-1], dtype=np.uint64, out=off[1:])
+    data = np.zeros(int(off[-1] + ln[-1]) + 64, np.uint8)
+    lib.shl_corpus_fill_host(seed, first, n, kind, off.ctypes.data, data.ctypes.data)
+    return Arena(data, off, ln)
+
+
+def test_c4_device_corpus_batches_weighted_ring(eng):
+    """Config 4 shape at reduced size: requests generated IN HBM batch by batch (as a rank of the
+    100 M-request job does), 256-node x 160-point weighted ring, histogram accumulated on the
+    device across batches; checked against the oracle over the host copy of the same corpus."""
+    hosts = ['10.1.%d.%d' % (i // 250, i % 250 + 1) for i in range(256)]
+    eng.ring_build(hosts, mode=N.RING_KETAMA_WEIGHTED)
+    vals, nodes = eng.ring_export()
+    ov, on = O.orc_ring(hosts, [11211] * 256, [1] * 256, 1)
+    assert len(vals) == 40960 and (vals == ov).all() and (nodes == on).all()
+    seed, per, nb = 20130727, 1 << 17, 4
+    hist = np.zeros(256, np.uint64)
+    ohist = np.zeros(256, np.uint64)
+    for b in range(nb):
+        db = eng.corpus_dev(seed, b * per, per, 0)
+        har = _host_corpus(eng.lib, seed, b * per, per, 0)
+        if b == 0:                                             # device bytes == host bytes for the same (seed, i)
+            dev_bytes = db.fetch(db.d_arena, np.uint8, db.nbytes)
+            assert db.nbytes == har.nbytes and (dev_bytes == har.data[:har.nbytes]).all()
+            assert (db.len == har.len).all()
+        db.route(256)
+        eng.sync()
+        st = db.field('status')
+        assert ((st & 0xff) == 0).all()
+        node = db.fetch(db.d_node, np.uint32, per)
+        hist += db.fetch(db.d_hist, np.uint64, 256)
+        o = O.orc_parse(har, hdr_cap=per * 24)
+        oq = O.orc_place(har, ov, on, 256, (har.off + o.sp1[:per] + 1).astype(np.uint64), (o.sp2[:per] - o.sp1[:per] - 1).astype(np.uint32))
+        assert (node == oq.node[:per]).all()
+        assert (db.field('sp1') == o.sp1[:per]).all() and (db.field('n_headers') == o.n_headers[:per]).all()
+        ohist += oq.hist
+        db.free()
+    assert hist.tolist() == ohist.tolist() and int(hist.sum()) == per * nb
+
+
+def test_c5_remap_sweep_1024_nodes(eng):
+    """Config 5 at reduced size: keys-only corpus, 1024-node ring (102 400 points); remove host
+    0 / 511 / 1023 and append a new one, rebuild, re-place; node IDENTITY (host string) must equal
+    the oracle's for every key, and about 1/1024 of the keys move."""
+    n = 1 << 19
+    base_hosts = ['10.%d.%d.%d' % (2 + i // 62500, (i // 250) % 250, i % 250 + 1) for i in range(1024)]
+    db = eng.corpus_dev(20130728, 0, n, 1)
+    har = _host_corpus(eng.lib, 20130728, 0, n, 1)
+    assert (db.fetch(db.d_arena, np.uint8, db.nbytes) == har.data[:har.nbytes]).all()
+
+    def place(hosts):
+        eng.ring_build(hosts)
+        ov, on = O.orc_ring(hosts, [11211] * len(hosts))
+        v, nd = eng.ring_export()
+        assert (v == ov).all() and (nd == on).all()
+        db.q = None                                           # fresh histogram / node arrays per ring size
+        db.place(len(hosts))
+        eng.sync()
+        node = db.fetch(db.d_node, np.uint32, n)
+        oq = O.orc_place(har, ov, on, len(hosts))
+        assert (node == oq.node[:n]).all()
+        assert db.fetch(db.d_hist, np.uint64, len(hosts)).tolist() == oq.hist.tolist()
+        return np.array(hosts, dtype=object)[node]
+
+    owner0 = place(base_hosts)
+    assert len(eng.ring_export()[0]) == 102400
+    for k in (0, 511, 1023):
+        hosts = base_hosts[:k] + base_hosts[k + 1:] + ['10.9.9.%d' % (k % 250 + 1)]
+        owner = place(hosts)
+        moved = owner != owner0
+        was_on_removed = owner0 == base_hosts[k]
+        assert moved[was_on_removed].all()                     # every key of the removed host moves
+        frac = float(moved.mean())
+        assert 0.5 / 1024 < frac < 4.0 / 1024, frac            # removed host's share + the new host's share
+        assert set(owner[moved & ~was_on_removed]) <= {hosts[-1]}   # anything else that moved went to the new host
+    db.free()
