@@ -23,6 +23,7 @@
 // Anything off the canonical shape (responses' first line, whitespace around the header block,
 // more lines than the lists hold) takes a per-lane scalar path with the same semantics.
 #pragma once
+#include <cuda_fp16.h>
 #include "shl_device.cuh"
 
 namespace shl {
@@ -195,49 +196,63 @@ __device__ __forceinline__ uint32_t ld32u(const uint8_t* p) {
 struct LaneScan { int idx, T; uint32_t n_c, n_s; bool ovf; };
 
 // cr[k * 32] / sp[k * 32]: this lane's slots of the warp's position lists (u16, lane-interleaved).
-__device__ __forceinline__ void scan_lists(const uint8_t* m, const int L, uint16_t* cr, uint16_t* sp, const SwarK& K, LaneScan& o) {
+// 0xFFFF in each 16-bit half of x that equals the matching half of pat.  The halves are compared
+// as fp16 numbers by ONE HSET2 on the FMA/half pipe; that is exact here because both patterns
+// (0x0A0D = "\r\n", 0x203A = ": ", little-endian) are normal, non-zero fp16 values, so numeric
+// equality is bit equality (NaN halves compare false, +-0 and denormals are not the patterns).
+__device__ __forceinline__ uint32_t eq16x2(uint32_t x, uint32_t pat) {
+    return __heq2_mask(*reinterpret_cast<const __half2*>(&x), *reinterpret_cast<const __half2*>(&pat));
+}
+
+// Event bits of one 32-bit word w (nx = the word that follows it in memory), position-ordered:
+// bit 2j = ": " starts at byte j, bit 2j+1 = CRLF starts at byte j.
+__device__ __forceinline__ uint32_t pair_events(uint32_t w, uint32_t nx) {
+    const uint32_t sh = __funnelshift_r(w, nx, 8);                     // bytes 1..4: the odd alignment
+    const uint32_t fc = __byte_perm(eq16x2(w, 0x0A0D0A0Du), eq16x2(sh, 0x0A0D0A0Du), 0x6240);   // 0xFF per byte that starts a CRLF
+    const uint32_t fs = __byte_perm(eq16x2(w, 0x203A203Au), eq16x2(sh, 0x203A203Au), 0x6240);   // ... that starts a ": "
+    return __umulhi((fc & 0x80808080u) | (fs & 0x40404040u), 0x04104100u);   // [s0 c0 s1 c1 s2 c2 s3 c3] + stray bits above bit 7
+}
+
+__device__ __forceinline__ void scan_lists(const uint8_t* m, const int L, uint16_t* cr, uint16_t* sp, LaneScan& o) {
     const int lead = (int)(reinterpret_cast<uintptr_t>(m) & 31);
     const uint4* vp = reinterpret_cast<const uint4*>(m - lead);
-    const int nsec = (lead + L + 31) >> 5;
+    const int nvec = 2 * ((lead + L + 31) >> 5);
     int p = -lead;                                 // message position of byte 0 of the current vector
     int idx = -1, T = -1, last_cr = -4;
-    uint32_t n_c = 0, n_s = 0, prev_cr = 0, prev_co = 0;
-    bool ovf = false;
+    uint32_t n_c = 0, n_s = 0;
     uint4 v = __ldg(vp), v1 = __ldg(vp + 1);
-    for (int i = 0; i < 2 * nsec; i++, p += 16) {
+    for (int i = 0; i < nvec && p < L; i++, p += 16) {
         uint4 nx = make_uint4(0u, 0u, 0u, 0u);
-        if (i + 2 < 2 * nsec) nx = __ldg(vp + i + 2);                // two vectors (one sector) ahead
-        if (p < L) {
-            const uint32_t cr0 = eqf(v.x, K.cr, K), cr1 = eqf(v.y, K.cr, K), cr2 = eqf(v.z, K.cr, K), cr3 = eqf(v.w, K.cr, K);
-            const uint32_t co0 = eqf(v.x, K.col, K), co1 = eqf(v.y, K.col, K), co2 = eqf(v.z, K.col, K), co3 = eqf(v.w, K.col, K);
-            uint32_t c16 = mask16(eqf_and(v.x, K.lf, __funnelshift_l(prev_cr, cr0, 8), K), eqf_and(v.y, K.lf, __funnelshift_l(cr0, cr1, 8), K),
-                                  eqf_and(v.z, K.lf, __funnelshift_l(cr1, cr2, 8), K), eqf_and(v.w, K.lf, __funnelshift_l(cr2, cr3, 8), K));
-            uint32_t s16 = mask16(eqf_and(v.x, K.sp, __funnelshift_l(prev_co, co0, 8), K), eqf_and(v.y, K.sp, __funnelshift_l(co0, co1, 8), K),
-                                  eqf_and(v.z, K.sp, __funnelshift_l(co1, co2, 8), K), eqf_and(v.w, K.sp, __funnelshift_l(co2, co3, 8), K));
-            prev_cr = cr3; prev_co = co3;
-            if (p < 1 || p + 16 > L) { const uint32_t vm = rng16(1 - p, L - p); c16 &= vm; s16 &= vm; }   // pair ends live in [1, L)
-            while (s16) {                          // ": " positions (of the ':')
-                const int k = __ffs(s16) - 1;
-                s16 &= s16 - 1u;
-                if (n_s >= (uint32_t)kSepCap) { ovf = true; break; }
-                sp[n_s * 32] = (uint16_t)(p + k - 1);
-                n_s++;
-            }
-            while (c16) {                          // CRLF positions (of the CR)
-                const int k = __ffs(c16) - 1;
-                c16 &= c16 - 1u;
-                const int pos = p + k - 1;
-                if (pos == last_cr + 2 && n_c >= 2u) { T = last_cr; break; }     // empty line after the first line: CRLFCRLF
-                if (n_c >= (uint32_t)kCrCap) { ovf = true; break; }
-                idx = n_c ? idx : pos;
-                cr[n_c * 32] = (uint16_t)pos;
-                n_c++; last_cr = pos;
-            }
-            if (T >= 0 || ovf) break;
+        if (i + 2 < nvec) nx = __ldg(vp + i + 2);                      // one 32-byte sector ahead
+        uint32_t ev = (pair_events(v.x, v.y) & 0xffu) | ((pair_events(v.y, v.z) & 0xffu) << 8) |
+                      ((pair_events(v.z, v.w) & 0xffu) << 16) | (pair_events(v.w, v1.x) << 24);
+        if (p < 0 || p + 17 > L) {                 // a pair may start at message positions [0, L-1)
+            const int lo = clamp16(-p), hi = clamp16(L - 1 - p);
+            const uint32_t mhi = hi >= 16 ? 0xffffffffu : (1u << (2 * hi)) - 1u;
+            const uint32_t mlo = lo >= 16 ? 0xffffffffu : (1u << (2 * lo)) - 1u;
+            ev &= mhi & ~mlo;
         }
+        uint32_t sb = ev & 0x55555555u, cb = ev & 0xaaaaaaaau;
+        while (sb) {                               // ": " positions (of the ':')
+            const int b = __ffs(sb) - 1;
+            sb &= sb - 1u;
+            sp[min(n_s, (uint32_t)kSepCap - 1u) * 32] = (uint16_t)(p + (b >> 1));
+            n_s++;
+        }
+        while (cb) {                               // CRLF positions (of the CR)
+            const int b = __ffs(cb) - 1;
+            cb &= cb - 1u;
+            const int pos = p + (b >> 1);
+            if (pos == last_cr + 2 && n_c >= 2u) { T = last_cr; break; }     // empty line after the first line: CRLFCRLF
+            idx = n_c ? idx : pos;
+            cr[min(n_c, (uint32_t)kCrCap - 1u) * 32] = (uint16_t)pos;
+            n_c++; last_cr = pos;
+        }
+        if (T >= 0) break;
         v = v1; v1 = nx;
     }
-    o.idx = idx; o.T = T; o.n_c = n_c; o.n_s = n_s; o.ovf = ovf;
+    o.idx = idx; o.T = T; o.n_c = n_c; o.n_s = n_s;
+    o.ovf = n_c > (uint32_t)kCrCap || n_s > (uint32_t)kSepCap;       // the lists are incomplete: scalar path
 }
 
 // ----------------------------------------------------------------------------------- epilogue helpers
@@ -307,7 +322,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 8) k_route(const RouteArg
 
         // ---- scan (lanes diverge on their own events; nothing heavy happens in here)
         LaneScan sc; sc.idx = sc.T = -1; sc.n_c = sc.n_s = 0; sc.ovf = false;
-        if (L > 0) scan_lists(m, L, cr, sp, K, sc);
+        if (L > 0) scan_lists(m, L, cr, sp, sc);
 
         // ---- first line, header block bounds, line count
         Msg r;
