@@ -13,7 +13,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'libshellac_b200.so')
+LIB_PATH = os.environ.get('SHL_LIB') or os.path.join(_HERE, 'libshellac_b200.so')
 
 # ---------------------------------------------------------------------------- status word
 S_OK, S_EMPTY, S_INCOMPLETE_LINE, S_INCOMPLETE_HEADERS, S_INCOMPLETE_BODY = 0, 1, 2, 3, 4

@@ -39,7 +39,7 @@ struct shl_ctx {
     uint64_t* h_counters = nullptr;       // pinned mirror
     int32_t* d_ch_len = nullptr; uint64_t* d_ch_size = nullptr; uint8_t* d_ch_ok = nullptr;
     // ring
-    uint32_t* d_ring_values = nullptr; uint32_t* d_ring_nodes = nullptr;
+    uint32_t* d_ring_values = nullptr; uint32_t* d_ring_nodes = nullptr; uint32_t* d_ring_dir = nullptr;
     std::vector<uint32_t> ring_values, ring_nodes;
     uint32_t n_points = 0, n_hosts = 0;
     uint64_t* d_hist = nullptr; uint32_t hist_cap = 0;
@@ -198,7 +198,7 @@ void shl_ctx_destroy(shl_ctx* ctx) {
     cudaFree(ctx->dq.md5); cudaFree(ctx->dq.hash); cudaFree(ctx->dq.node);
     cudaFree(ctx->d_ch_len); cudaFree(ctx->d_ch_size); cudaFree(ctx->d_ch_ok);
     cudaFree(ctx->d_counters); cudaFreeHost(ctx->h_counters);
-    cudaFree(ctx->d_ring_values); cudaFree(ctx->d_ring_nodes); cudaFree(ctx->d_hist);
+    cudaFree(ctx->d_ring_values); cudaFree(ctx->d_ring_nodes); cudaFree(ctx->d_ring_dir); cudaFree(ctx->d_hist);
     for (auto& e : ctx->ev) cudaEventDestroy(e);
     for (auto& st : ctx->pipe) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
     cudaEventDestroy(ctx->ev_fork);
@@ -305,6 +305,19 @@ int shl_ring_build(shl_ctx* ctx, const char* const* hosts, const uint32_t* ports
     CU(dalloc(&ctx->d_ring_values, pts.size())); CU(dalloc(&ctx->d_ring_nodes, pts.size()));
     CU(cudaMemcpy(ctx->d_ring_values, ctx->ring_values.data(), pts.size() * 4, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(ctx->d_ring_nodes, ctx->ring_nodes.data(), pts.size() * 4, cudaMemcpyHostToDevice));
+    {   // directory on the top kRingDirBits hash bits: dir[b] = first point with value >= b << (32 - bits)
+        const uint32_t nb = 1u << shl::kRingDirBits;
+        std::vector<uint32_t> dir(nb + 1);
+        size_t j = 0;
+        for (uint32_t b = 0; b < nb; b++) {
+            const uint32_t base = b << (32 - shl::kRingDirBits);
+            while (j < pts.size() && ctx->ring_values[j] < base) j++;
+            dir[b] = (uint32_t)j;
+        }
+        dir[nb] = (uint32_t)pts.size();
+        if (!ctx->d_ring_dir) CU(dalloc(&ctx->d_ring_dir, nb + 1));
+        CU(cudaMemcpy(ctx->d_ring_dir, dir.data(), (nb + 1) * 4, cudaMemcpyHostToDevice));
+    }
     ctx->n_points = (uint32_t)pts.size(); ctx->n_hosts = n_hosts;
     if (ctx->hist_cap < n_hosts) {
         cudaFree(ctx->d_hist); ctx->d_hist = nullptr;
@@ -348,7 +361,7 @@ static int launch_route(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_
     const uint64_t groups = (n + shl::kGroup - 1) / shl::kGroup;
     const unsigned blocks = (unsigned)((groups + shl::kWarpsPerBlock - 1) / shl::kWarpsPerBlock);
     if (d_q) {
-        a.ring_values = ctx->d_ring_values; a.ring_nodes = ctx->d_ring_nodes;
+        a.ring_values = ctx->d_ring_values; a.ring_nodes = ctx->d_ring_nodes; a.ring_dir = ctx->d_ring_dir;
         a.n_points = ctx->n_points; a.n_hosts = ctx->n_hosts; a.place = *d_q;
         const size_t sh = (d_q->hist && ctx->n_hosts <= 4096u) ? ctx->n_hosts * 4 : 0;
         shl::k_route<true><<<blocks, shl::kWarpsPerBlock * 32, sh, stream>>>(a);
@@ -388,7 +401,8 @@ int shl_place_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_key_of
     if (n == 0) return SHL_OK;
     shl::PlaceArgs a{};
     a.arena = d_arena; a.key_off = d_key_off; a.key_len = d_key_len; a.n = n;
-    a.ring_values = ctx->d_ring_values; a.ring_nodes = ctx->d_ring_nodes; a.n_points = ctx->n_points; a.n_hosts = ctx->n_hosts;
+    a.ring_values = ctx->d_ring_values; a.ring_nodes = ctx->d_ring_nodes; a.ring_dir = ctx->d_ring_dir;
+    a.n_points = ctx->n_points; a.n_hosts = ctx->n_hosts;
     a.out = *d_out;
     const size_t sh = (d_out->hist && ctx->n_hosts <= 4096u) ? ctx->n_hosts * 4 : 0;
     shl::k_place<<<(unsigned)((n + 255) / 256), 256, sh, ctx->stream>>>(a);

@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(128) k_chunk_header(const uint8_t* arena, cons
 // key -> MD5 -> LE32 -> continuum lower-bound -> node (+ per-node histogram), one key per thread.
 struct PlaceArgs {
     const uint8_t* arena; const uint64_t* key_off; const uint32_t* key_len; uint64_t n;
-    const uint32_t* ring_values; const uint32_t* ring_nodes; uint32_t n_points, n_hosts;
+    const uint32_t* ring_values; const uint32_t* ring_nodes; const uint32_t* ring_dir; uint32_t n_points, n_hosts;
     shl_place_out out;
 };
 
@@ -146,7 +146,7 @@ __global__ void __launch_bounds__(256) k_place(const PlaceArgs a) {
     if (i < a.n) {
         uint32_t h[4];
         md5_key(a.arena + a.key_off[i], a.key_len[i], h);
-        const uint32_t node = ring_lookup(a.ring_values, a.ring_nodes, a.n_points, a.n_hosts, h[0]);
+        const uint32_t node = ring_lookup(a.ring_values, a.ring_nodes, a.ring_dir, a.n_points, a.n_hosts, h[0]);
         if (a.out.md5) {
             uint32_t* d = reinterpret_cast<uint32_t*>(a.out.md5) + 4 * i;
             d[0] = h[0]; d[1] = h[1]; d[2] = h[2]; d[3] = h[3];

@@ -28,6 +28,18 @@
 
 namespace shl {
 
+#ifndef SHL_OPT_PF_L2
+#define SHL_OPT_PF_L2 0
+#endif
+#ifndef SHL_OPT_PF_URL
+#define SHL_OPT_PF_URL 0
+#endif
+#ifndef SHL_OPT_RINGDIR
+#define SHL_OPT_RINGDIR 1
+#endif
+#ifndef SHL_OPT_BATCH
+#define SHL_OPT_BATCH 2
+#endif
 constexpr int kWarpsPerBlock = 4;
 constexpr int kGroup = 32;            // messages per warp (one per lane)
 constexpr int kCrCap = 24;            // CRLF positions a lane can list (first line + 23 header lines)
@@ -80,7 +92,7 @@ struct RouteArgs {
     SwarK k;                          // SWAR byte constants, as run-time values (see SwarK)
     uint32_t hdr_base_bias;           // added to the stored hdr_base (out.hdr may be a slice of a larger arena)
     // fused placement (route); ring_values == nullptr -> parse only
-    const uint32_t* ring_values; const uint32_t* ring_nodes; uint32_t n_points, n_hosts;
+    const uint32_t* ring_values; const uint32_t* ring_nodes; const uint32_t* ring_dir; uint32_t n_points, n_hosts;
     shl_place_out place;
 };
 
@@ -213,6 +225,9 @@ __device__ __forceinline__ uint32_t pair_events(uint32_t w, uint32_t nx) {
     return __umulhi((fc & 0x80808080u) | (fs & 0x40404040u), 0x04104100u);   // [s0 c0 s1 c1 s2 c2 s3 c3] + stray bits above bit 7
 }
 
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
+
 __device__ __forceinline__ void scan_lists(const uint8_t* m, const int L, uint16_t* cr, uint16_t* sp, LaneScan& o) {
     const int lead = (int)(reinterpret_cast<uintptr_t>(m) & 31);
     const uint4* vp = reinterpret_cast<const uint4*>(m - lead);
@@ -224,6 +239,9 @@ __device__ __forceinline__ void scan_lists(const uint8_t* m, const int L, uint16
     for (int i = 0; i < nvec && p < L; i++, p += 16) {
         uint4 nx = make_uint4(0u, 0u, 0u, 0u);
         if (i + 2 < nvec) nx = __ldg(vp + i + 2);                      // one 32-byte sector ahead
+#if SHL_OPT_PF_L2
+        if ((i & 7) == 0 && i + 16 < nvec) prefetch_l2(vp + i + 16);   // and the line after next on its way to L2
+#endif
         uint32_t ev = (pair_events(v.x, v.y) & 0xffu) | ((pair_events(v.y, v.z) & 0xffu) << 8) |
                       ((pair_events(v.z, v.w) & 0xffu) << 16) | (pair_events(v.w, v1.x) << 24);
         if (p < 0 || p + 17 > L) {                 // a pair may start at message positions [0, L-1)
@@ -309,9 +327,10 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 8) k_route(const RouteArg
     if (smem_hist) for (uint32_t i = threadIdx.x; i < a.n_hosts; i += blockDim.x) s_hist[i] = 0u;
     __syncthreads();
 
-    const uint64_t first = ((uint64_t)blockIdx.x * kWarpsPerBlock + warp) * kGroup;
-    if (first < a.n) {
-        const uint64_t mine = first + lane;
+    // (A block-level counting sort of the messages by scan length, so that the lanes of a warp
+    // finish together, was tried here: 1.6 % faster and one more thing to get wrong.  Not kept.)
+    {
+        const uint64_t mine = ((uint64_t)blockIdx.x * kWarpsPerBlock + warp) * kGroup + lane;
         const bool have = mine < a.n;
         const uint64_t my_off = have ? a.off[mine] : 0ull;
         const int L = have ? (int)min(a.len[mine], 0x7fffffc0u) : 0;
@@ -348,6 +367,11 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 8) k_route(const RouteArg
                 }
                 if (fl_code) r.status |= fl_code;
                 else {
+                    if (SHL_OPT_PF_URL && kPlace && (r.status & SHL_F_IS_REQUEST)) {     // the URL is hashed at the very end: start fetching it now
+                        prefetch_l1(m + r.sp1 + 1);
+                        if (r.sp2 - r.sp1 > 32u) prefetch_l1(m + r.sp1 + 33);
+                        if (r.sp2 - r.sp1 > 64u) prefetch_l1(m + r.sp1 + 65);
+                    }
                     h0 = idx + 2;
                     T = sc.ovf ? find_term_scalar(m, h0, L) : sc.T;
                     if (T < 0) r.status |= SHL_S_INCOMPLETE_HEADERS;
@@ -403,21 +427,37 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 8) k_route(const RouteArg
                 w2.n_te = w2.n_cl = 0; w2.te_vs = w2.te_ve = w2.cl_vs = w2.cl_ve = 0;
                 headers_scalar(m, h0, T + 4, out, 1, nh, &n2, &w2);
             } else {
+                // four lines per round: all eight byte peeks are in flight before the first is needed
                 int ls = h0;
-                for (uint32_t k = 0; k < nh; k++) {
-                    const int sep = sp[k * 32], end = cr[(k + 1) * 32];
-                    int vs = sep + 2, ve = end;
-                    const uint32_t c0 = vs < ve ? ldb(m + vs) : 'x', c1 = ve > vs ? ldb(m + ve - 1) : 'x';
-                    if (is_ws(c0) || is_ws(c1)) {
-                        while (vs < ve && is_ws(ldb(m + vs))) vs++;
-                        while (ve > vs && is_ws(ldb(m + ve - 1))) ve--;
+                constexpr int kB = SHL_OPT_BATCH;
+                for (uint32_t k0 = 0; k0 < nh; k0 += kB) {
+                    int sepv[kB], endv[kB];
+                    uint32_t c0v[kB], c1v[kB];
+#pragma unroll
+                    for (int j = 0; j < kB; j++) {
+                        sepv[j] = endv[j] = 0; c0v[j] = c1v[j] = 'x';
+                        if (k0 + j < nh) {
+                            sepv[j] = sp[(k0 + j) * 32]; endv[j] = cr[(k0 + j + 1) * 32];
+                            if (sepv[j] + 2 < endv[j]) { c0v[j] = ldb(m + sepv[j] + 2); c1v[j] = ldb(m + endv[j] - 1); }
+                        }
                     }
-                    const int klen = sep - ls;
-                    const uint32_t lo = (uint32_t)ls | ((uint32_t)klen << 16), hi = (uint32_t)vs | ((uint32_t)(ve - vs) << 16);
-                    *reinterpret_cast<uint2*>(out + k) = make_uint2(lo, hi);
-                    if (klen == 14) { if (span_eq_lower(m, ls, sep, "content-length")) { if (!wk.n_cl) { wk.cl_vs = vs; wk.cl_ve = ve; } wk.n_cl++; } }
-                    else if (klen == 17) { if (span_eq_lower(m, ls, sep, "transfer-encoding")) { if (!wk.n_te) { wk.te_vs = vs; wk.te_ve = ve; } wk.n_te++; } }
-                    ls = end + 2;
+#pragma unroll
+                    for (int j = 0; j < kB; j++) {
+                        if (k0 + j < nh) {
+                            const int sep = sepv[j], end = endv[j];
+                            int vs = sep + 2, ve = end;
+                            if (is_ws(c0v[j]) || is_ws(c1v[j])) {
+                                while (vs < ve && is_ws(ldb(m + vs))) vs++;
+                                while (ve > vs && is_ws(ldb(m + ve - 1))) ve--;
+                            }
+                            const int klen = sep - ls;
+                            const uint32_t lo = (uint32_t)ls | ((uint32_t)klen << 16), hi = (uint32_t)vs | ((uint32_t)(ve - vs) << 16);
+                            *reinterpret_cast<uint2*>(out + k0 + j) = make_uint2(lo, hi);
+                            if (klen == 14) { if (span_eq_lower(m, ls, sep, "content-length")) { if (!wk.n_cl) { wk.cl_vs = vs; wk.cl_ve = ve; } wk.n_cl++; } }
+                            else if (klen == 17) { if (span_eq_lower(m, ls, sep, "transfer-encoding")) { if (!wk.n_te) { wk.te_vs = vs; wk.te_ve = ve; } wk.n_te++; } }
+                            ls = end + 2;
+                        }
+                    }
                 }
             }
             r.n_headers = nh;
@@ -446,7 +486,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 8) k_route(const RouteArg
             uint32_t h[4] = {0u, 0u, 0u, 0u}, node = 0xffffffffu;
             if (routable) {
                 md5_key(m + r.sp1 + 1u, r.sp2 - r.sp1 - 1u, h);
-                node = ring_lookup(a.ring_values, a.ring_nodes, a.n_points, a.n_hosts, h[0]);
+                node = ring_lookup(a.ring_values, a.ring_nodes, SHL_OPT_RINGDIR ? a.ring_dir : nullptr, a.n_points, a.n_hosts, h[0]);
                 if (a.place.hist) {
                     if (smem_hist) atomicAdd(&s_hist[node], 1u);
                     else atomicAdd(reinterpret_cast<unsigned long long*>(a.place.hist) + node, 1ull);

@@ -133,6 +133,29 @@ def test_golden_vs_oracle_soa_all_alignments(eng, golden):
         assert_frame_equal(ar, eng.frame(ar, g, reuse_arena=True), O.orc_frame(ar, o), 'golden frame %d' % rep)
 
 
+def test_fresh_engines_give_the_same_records_every_time(golden):
+    """Regression guard for allocation races: a fresh ctx per iteration (so stale device memory
+    would show), records and record ranges checked against the oracle each time."""
+    from shellac_b200.engine import Engine
+    msgs = [w['msg'] for w in golden['whole']]
+    o = None
+    for it in range(12):
+        e = Engine(device=0, max_msgs=1 << 14, max_bytes=1 << 24, max_records=1 << 20)
+        try:
+            ar = e.pack(msgs)
+            if o is None:
+                o = O.orc_parse(ar)
+            g = e.parse(ar)
+            assert_parse_equal(ar, g, o, 'fresh engine %d' % it)
+            n = ar.n
+            base, cnt = g.hdr_base[:n].astype(np.int64), g.n_headers[:n].astype(np.int64)
+            order = np.argsort(base, kind='stable')
+            b, c = base[order][cnt[order] > 0], cnt[order][cnt[order] > 0]
+            assert (b[1:] >= b[:-1] + c[:-1]).all(), 'record ranges overlap'
+        finally:
+            e.close()
+
+
 def test_golden_streams_and_gzip(eng, golden):
     for s in golden['streams']:
         data, start = s['stream'], 0
