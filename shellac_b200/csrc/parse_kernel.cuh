@@ -15,8 +15,9 @@
 //            but append their positions to two lane-private, lane-interleaved u16 lists in
 //            shared memory; two consecutive CRLFs after the first line end the scan.  The loop
 //            body that runs under divergence is a dozen instructions.
-//   epilogue lanes are converged again: first-line evaluation, a sorted merge of the two lists
-//            (line k must hold exactly one ": "), one atomic record allocation per group, value
+//            The same loop notes the first two spaces while on the first line and checks, as
+//            CRLFs arrive, that each header line held exactly one ": ".
+//   epilogue lanes are converged again: first-line evaluation, one atomic record allocation per group, value
 //            strip + record write, Content-Length / Transfer-Encoding decision, struct-of-arrays
 //            stores (lane j == message j, so they are coalesced), MD5 + continuum search +
 //            shared-memory histogram.
@@ -36,6 +37,9 @@ namespace shl {
 #endif
 #ifndef SHL_OPT_RINGDIR
 #define SHL_OPT_RINGDIR 1
+#endif
+#ifndef SHL_OPT_MINBLOCKS
+#define SHL_OPT_MINBLOCKS 8
 #endif
 #ifndef SHL_OPT_BATCH
 #define SHL_OPT_BATCH 2
@@ -205,7 +209,7 @@ __device__ __forceinline__ uint32_t ld32u(const uint8_t* p) {
 }
 
 // ----------------------------------------------------------------------------------- scan: one message, one lane
-struct LaneScan { int idx, T; uint32_t n_c, n_s; bool ovf; };
+struct LaneScan { int idx, T, sp1, sp2; uint32_t n_c, n_s, s_skip, first_bad, bad_cnt; bool ovf; };
 
 // cr[k * 32] / sp[k * 32]: this lane's slots of the warp's position lists (u16, lane-interleaved).
 // 0xFFFF in each 16-bit half of x that equals the matching half of pat.  The halves are compared
@@ -228,13 +232,14 @@ __device__ __forceinline__ uint32_t pair_events(uint32_t w, uint32_t nx) {
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
 __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
 
-__device__ __forceinline__ void scan_lists(const uint8_t* m, const int L, uint16_t* cr, uint16_t* sp, LaneScan& o) {
+__device__ __forceinline__ void scan_lists(const uint8_t* m, const int L, uint16_t* cr, uint16_t* sp, const SwarK& K, LaneScan& o) {
     const int lead = (int)(reinterpret_cast<uintptr_t>(m) & 31);
     const uint4* vp = reinterpret_cast<const uint4*>(m - lead);
     const int nvec = 2 * ((lead + L + 31) >> 5);
     int p = -lead;                                 // message position of byte 0 of the current vector
-    int idx = -1, T = -1, last_cr = -4;
+    int idx = -1, T = -1, last_cr = -4, sp1 = -1, sp2 = -1;
     uint32_t n_c = 0, n_s = 0;
+    uint32_t s_skip = 0, s_prev = 0, first_bad = 0xffffffffu, bad_cnt = 0;   // on-line "exactly one ': ' per line" check
     uint4 v = __ldg(vp), v1 = __ldg(vp + 1);
     for (int i = 0; i < nvec && p < L; i++, p += 16) {
         uint4 nx = make_uint4(0u, 0u, 0u, 0u);
@@ -251,6 +256,14 @@ __device__ __forceinline__ void scan_lists(const uint8_t* m, const int L, uint16
             ev &= mhi & ~mlo;
         }
         uint32_t sb = ev & 0x55555555u, cb = ev & 0xaaaaaaaau;
+        if (idx < 0) {                             // still on the first line: note its first two spaces
+            uint32_t z = mask16(eqf(v.x, K.sp, K), eqf(v.y, K.sp, K), eqf(v.z, K.sp, K), eqf(v.w, K.sp, K));
+            if (p < 0 || p + 16 > L) z &= rng16(-p, L - p);
+            if (cb) z &= below((__ffs(cb) - 1) >> 1);
+            if (z && sp1 < 0) { sp1 = p + __ffs(z) - 1; z &= z - 1u; }
+            if (z && sp1 >= 0 && sp2 < 0) sp2 = p + __ffs(z) - 1;
+        }
+        const uint32_t sb0 = sb, n_s0 = n_s;
         while (sb) {                               // ": " positions (of the ':')
             const int b = __ffs(sb) - 1;
             sb &= sb - 1u;
@@ -262,39 +275,30 @@ __device__ __forceinline__ void scan_lists(const uint8_t* m, const int L, uint16
             cb &= cb - 1u;
             const int pos = p + (b >> 1);
             if (pos == last_cr + 2 && n_c >= 2u) { T = last_cr; break; }     // empty line after the first line: CRLFCRLF
-            idx = n_c ? idx : pos;
+            const uint32_t seen = n_s0 + (uint32_t)__popc(sb0 & ((1u << b) - 1u));   // ": " before this CR
+            if (n_c == 0u) { idx = pos; s_skip = seen; }
+            else if (seen - s_prev != 1u && first_bad == 0xffffffffu) { first_bad = n_c - 1u; bad_cnt = seen - s_prev; }
+            s_prev = seen;
             cr[min(n_c, (uint32_t)kCrCap - 1u) * 32] = (uint16_t)pos;
             n_c++; last_cr = pos;
         }
         if (T >= 0) break;
         v = v1; v1 = nx;
     }
-    o.idx = idx; o.T = T; o.n_c = n_c; o.n_s = n_s;
+    o.idx = idx; o.T = T; o.n_c = n_c; o.n_s = n_s; o.sp1 = sp1; o.sp2 = sp2;
+    o.s_skip = s_skip; o.first_bad = first_bad; o.bad_cnt = bad_cnt;
     o.ovf = n_c > (uint32_t)kCrCap || n_s > (uint32_t)kSepCap;       // the lists are incomplete: scalar path
 }
 
 // ----------------------------------------------------------------------------------- epilogue helpers
 // Canonical request line  METHOD SP URL SP "HTTP/1.x" CRLF  (no other space, no trailing blank):
 // fills the first-line fields and returns true; anything else goes to first_line_scalar.
-__device__ __forceinline__ bool first_line_fast(const uint8_t* m, const int idx, const SwarK& K, Msg& r, bool& get_or_head) {
-    const int sp2 = idx - 9;
-    if (sp2 < 1) return false;
-    const uint32_t w0 = ld32u(m + sp2 + 1), w1 = ld32u(m + sp2 + 5);
-    if (ldb(m + sp2) != ' ' || w0 != 0x50545448u || (w1 != 0x312E312Fu && w1 != 0x302E312Fu)) return false;
-    // exactly one space in [0, sp2): SWAR over the aligned vectors that cover it
-    const int lead = (int)(reinterpret_cast<uintptr_t>(m) & 15);
-    const uint4* vp = reinterpret_cast<const uint4*>(m - lead);
-    const int nv = (lead + sp2 + 15) >> 4;
-    int nsp = 0, sp1 = -1, p = -lead;
-    for (int i = 0; i < nv; i++, p += 16) {
-        const uint4 v = __ldg(vp + i);
-        uint32_t z = mask16(eqf(v.x, K.sp, K), eqf(v.y, K.sp, K), eqf(v.z, K.sp, K), eqf(v.w, K.sp, K));
-        if (p < 0 || p + 16 > sp2) z &= rng16(-p, sp2 - p);
-        if (z && sp1 < 0) sp1 = p + __ffs(z) - 1;
-        nsp += __popc(z);
-    }
-    if (nsp != 1) return false;
-    const uint32_t f4 = ld32u(m);
+__device__ __forceinline__ bool first_line_fast(const uint8_t* m, const int idx, const int sp1, const int sp2, Msg& r, bool& get_or_head) {
+    // sp1 / sp2 are the first two spaces of the line (noted by the scan); the third part must be
+    // exactly the 8 bytes "HTTP/1.0" or "HTTP/1.1", which also rules out a trailing blank.
+    if (sp1 < 0 || sp2 <= sp1 || idx - sp2 - 1 != 8) return false;
+    const uint32_t w0 = ld32u(m + sp2 + 1), w1 = ld32u(m + sp2 + 5), f4 = ld32u(m);
+    if (w0 != 0x50545448u || (w1 != 0x312E312Fu && w1 != 0x302E312Fu)) return false;
     if ((f4 & 0xffffu) == 0x5448u && sp1 >= 2) return false;            // a.startswith('HT'): a response
     r.sp1 = (uint32_t)sp1; r.sp2 = (uint32_t)sp2; r.fl_end = (uint32_t)idx; r.slash = (uint32_t)(sp2 + 5);
     r.status = (r.status & ~SHL_F_VERSION_MASK) | ((w1 >> 24) == '1' ? 1u << SHL_F_VERSION_SHIFT : 0u) | SHL_F_FIRST_LINE_DONE;
@@ -314,7 +318,7 @@ __device__ __noinline__ int find_term_scalar(const uint8_t* m, int from, int L) 
 
 // ----------------------------------------------------------------------------------- kernel
 template <bool kPlace>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32, 8) k_route(const RouteArgs a) {
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_route(const RouteArgs a) {
     __shared__ uint16_t s_cr[kWarpsPerBlock][kCrCap * 32];
     __shared__ uint16_t s_sp[kWarpsPerBlock][kSepCap * 32];
     __shared__ uint32_t s_codes[64];
@@ -340,9 +344,13 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 8) k_route(const RouteArg
         const bool force = a.force_scalar != 0;
 
         // ---- scan (lanes diverge on their own events; nothing heavy happens in here)
-        LaneScan sc; sc.idx = sc.T = -1; sc.n_c = sc.n_s = 0; sc.ovf = false;
-        if (L > 0) scan_lists(m, L, cr, sp, sc);
+        LaneScan sc; sc.idx = sc.T = sc.sp1 = sc.sp2 = -1; sc.n_c = sc.n_s = sc.s_skip = sc.bad_cnt = 0; sc.first_bad = 0xffffffffu; sc.ovf = false;
+        if (L > 0) scan_lists(m, L, cr, sp, K, sc);
 
+#ifdef SHL_EXP_SCANONLY
+        if (have) { a.out.status[mine] = sc.n_c + sc.n_s + (uint32_t)sc.T + (uint32_t)sc.idx; }
+        if (SHL_EXP_SCANONLY) goto scan_done;
+#endif
         // ---- first line, header block bounds, line count
         Msg r;
         r.status = (3u << SHL_F_VERSION_SHIFT) | SHL_F_IS_REQUEST;
@@ -360,7 +368,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 8) k_route(const RouteArg
             else {
                 r.first_line_len = (uint32_t)(idx + 2);
                 uint32_t fl_code = 0;
-                if (force || !first_line_fast(m, idx, K, r, get_or_head)) {
+                if (force || sc.ovf || !first_line_fast(m, idx, sc.sp1, sc.sp2, r, get_or_head)) {
                     Msg t = r; bool goh = false;   // the cold path may keep its copy in local memory
                     fl_code = first_line_scalar(m, idx, t, goh);
                     r = t; get_or_head = goh;
@@ -385,18 +393,12 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 8) k_route(const RouteArg
                             hdr_err = headers_scalar(m, h0, T + 4, nullptr, 1, 0u, &n2, &w2);
                             wk = w2; n_hdr = n2;
                         } else {
-                            // sorted merge: line k = (cr[k-1] + 2, cr[k]) must hold exactly one ": ";
-                            // its position is compacted into sp[k-1]
-                            uint32_t j = 0;
-                            while (j < sc.n_s && (int)sp[j * 32] < h0) j++;
-                            for (uint32_t k = 1; k < sc.n_c; k++) {
-                                const uint32_t end = cr[k * 32];
-                                uint32_t cnt = 0, fs = 0;
-                                while (j < sc.n_s && sp[j * 32] < end) { if (!cnt) fs = sp[j * 32]; cnt++; j++; }
-                                if (cnt != 1u) { hdr_err = cnt ? (uint32_t)SHL_E_HDR_MULTI_SEP : (uint32_t)SHL_E_HDR_NO_SEP; break; }
-                                sp[(k - 1) * 32] = (uint16_t)fs;
-                                n_hdr++;
-                            }
+                            // the scan already checked "exactly one ': ' per line" as it went: lines
+                            // before the first offender are the records; line k's separator is the
+                            // (s_skip + k)-th listed one (s_skip = those inside the first line)
+                            const uint32_t n_lines = sc.n_c - 1u;
+                            n_hdr = min(n_lines, sc.first_bad);
+                            if (sc.first_bad < n_lines) hdr_err = sc.bad_cnt ? (uint32_t)SHL_E_HDR_MULTI_SEP : (uint32_t)SHL_E_HDR_NO_SEP;
                         }
                     }
                 }
@@ -437,8 +439,10 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 8) k_route(const RouteArg
                     for (int j = 0; j < kB; j++) {
                         sepv[j] = endv[j] = 0; c0v[j] = c1v[j] = 'x';
                         if (k0 + j < nh) {
-                            sepv[j] = sp[(k0 + j) * 32]; endv[j] = cr[(k0 + j + 1) * 32];
+                            sepv[j] = sp[(sc.s_skip + k0 + j) * 32]; endv[j] = cr[(k0 + j + 1) * 32];
+#ifndef SHL_EXP_NOPEEK
                             if (sepv[j] + 2 < endv[j]) { c0v[j] = ldb(m + sepv[j] + 2); c1v[j] = ldb(m + endv[j] - 1); }
+#endif
                         }
                     }
 #pragma unroll
@@ -497,6 +501,9 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 8) k_route(const RouteArg
             if (a.place.node) a.place.node[mine] = node;
         }
     }
+#ifdef SHL_EXP_SCANONLY
+scan_done:
+#endif
     __syncthreads();
     if (a.code_hist && threadIdx.x < 64 && s_codes[threadIdx.x])
         atomicAdd(reinterpret_cast<unsigned long long*>(a.code_hist) + threadIdx.x, (unsigned long long)s_codes[threadIdx.x]);
