@@ -122,6 +122,16 @@ typedef struct shl_frame_out {
     uint64_t* chunk_used;
 } shl_frame_out;
 
+/* Body gather result: message i's body is body[body_off[i] : body_off[i] + body_len[i]]
+ * (each body starts 16-byte aligned; body_used[0] = bytes of the arena handed out).            */
+typedef struct shl_body_out {
+    uint64_t* body_off;        /* [n]                                                              */
+    uint64_t* body_len;        /* [n] bytes _parse_body has written for this message               */
+    uint8_t*  body;            /* byte arena, `body_cap` bytes                                     */
+    uint64_t  body_cap;
+    uint64_t* body_used;       /* one element                                                      */
+} shl_body_out;
+
 /* Placement result (struct-of-arrays, n elements each). */
 typedef struct shl_place_out {
     uint8_t*  md5;             /* 16 bytes per key: RFC 1321 digest (libhashkit md5.c)              */
@@ -199,6 +209,13 @@ int  shl_route_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes,
 int  shl_chunk_header_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes,
                             const uint64_t* off, const uint32_t* len, uint64_t n,
                             int32_t* hdr_len, uint64_t* size, uint8_t* ok);
+/* shl_body_batch / shl_body_dev replace the body accumulation of HttpParser._parse_body
+ * (HttpParser.py:340-347; callers :213-214 for Content-Length bodies, :296-297 per chunk): the
+ * bytes the framing spans select are gathered into one contiguous body per message (identity
+ * content-coding; gzip inflate stays with the host's zlib as in the reference, :343-344).
+ * shl_body_batch works on the batch whose shl_parse_batch + shl_frame_batch results are still
+ * resident on this ctx (call it right after them, same n).                                       */
+int  shl_body_batch(shl_ctx* ctx, uint64_t n, const shl_body_out* out);
 /* In every *_batch call `arena` may be NULL: the bytes uploaded by the previous *_batch call on
  * this ctx are reused (parse, then frame the same arena, costs one H2D copy).                    */
 
@@ -215,6 +232,8 @@ int  shl_place_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_key_o
                    uint64_t n, const shl_place_out* d_out);
 int  shl_route_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_off, const uint32_t* d_len,
                    uint64_t n, const shl_parse_out* d_pout, const shl_place_out* d_qout);
+int  shl_body_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_off, const uint32_t* d_len,
+                  uint64_t n, const shl_parse_out* d_pout, const shl_frame_out* d_fout, const shl_body_out* d_out);
 
 /* Placement without any allocation.  It has no counterpart in the reference: it exists for callers
  * of THIS library that cannot call cudaMalloc (the proxy's reactor thread, where an allocation

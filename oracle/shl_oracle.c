@@ -457,3 +457,42 @@ int orc_place(const uint8_t* arena, const uint64_t* key_off, const uint32_t* key
     }
     return 0;
 }
+
+/* Body accumulation (HttpParser.py:213-214, 296-297, 340-347), identity content-coding: the bytes
+ * _parse_body has written once the driver loop is over.  Bodies are laid out back to back, each
+ * start rounded up to 16 bytes (the device allocates in the same granule, in arbitrary order). */
+int orc_body(const uint8_t* arena, const uint64_t* off, const uint32_t* len, uint64_t n,
+             const shl_parse_out* p, const shl_frame_out* f, const shl_body_out* out) {
+    uint64_t used = 0;
+    for (uint64_t i = 0; i < n; i++) {
+        const uint8_t* m = arena + off[i];
+        uint32_t st = p->status[i];
+        uint64_t blen = 0;
+        out->body_off[i] = used;
+        if ((st & SHL_F_HEADERS_COMPLETE) && SHL_CODE(st) < 16) {
+            int no_call = (st & SHL_F_IS_REQUEST) && (st & SHL_F_FIRST_LINE_DONE) &&
+                          (span_eq(m, 0, p->sp1[i], "GET") || span_eq(m, 0, p->sp1[i], "HEAD"));
+            if (!no_call) {
+                if (st & SHL_F_CHUNKED) {
+                    if (f->fstatus[i] != 0xff) {
+                        for (uint32_t k = 0; k < f->n_chunks[i]; k++) {
+                            shl_chunk_span c = f->chunk[f->chunk_base[i] + k];
+                            if (used + blen + c.data_len <= out->body_cap) memcpy(out->body + used + blen, m + c.data_off, c.data_len);
+                            blen += c.data_len;
+                        }
+                    }
+                } else if ((st & SHL_F_MESSAGE_COMPLETE) && !(st & SHL_F_CLEN_WIDE)) {
+                    int64_t body_off = (int64_t)p->first_line_len[i] + p->headers_len[i];
+                    int64_t avail = (int64_t)len[i] - body_off, cl = p->content_len[i];
+                    int64_t take = cl >= 0 ? (cl < avail ? cl : avail) : (avail + cl > 0 ? avail + cl : 0);
+                    if (used + (uint64_t)take <= out->body_cap) memcpy(out->body + used, m + body_off, (size_t)take);
+                    blen = (uint64_t)take;
+                }
+            }
+        }
+        out->body_len[i] = blen;
+        used += (blen + 15) & ~(uint64_t)15;
+    }
+    *out->body_used = used;
+    return 0;
+}

@@ -61,6 +61,11 @@ class FrameOutStruct(C.Structure):
                 ('chunk', C.c_void_p), ('chunk_cap', C.c_uint64), ('chunk_used', C.c_void_p)]
 
 
+class BodyOutStruct(C.Structure):
+    _fields_ = [('body_off', C.c_void_p), ('body_len', C.c_void_p), ('body', C.c_void_p),
+                ('body_cap', C.c_uint64), ('body_used', C.c_void_p)]
+
+
 class PlaceOutStruct(C.Structure):
     _fields_ = [('md5', C.c_void_p), ('hash', C.c_void_p), ('node', C.c_void_p), ('hist', C.c_void_p)]
 
@@ -114,6 +119,8 @@ def lib():
         'shl_frame_batch': (i32, [vp, vp, u64, vp, vp, u64, vp, vp, vp, C.POINTER(FrameOutStruct)]),
         'shl_place_batch': (i32, [vp, vp, u64, vp, vp, u64, C.POINTER(PlaceOutStruct)]),
         'shl_route_batch': (i32, [vp, vp, u64, vp, vp, u64, C.POINTER(ParseOutStruct), C.POINTER(PlaceOutStruct)]),
+        'shl_body_batch': (i32, [vp, u64, C.POINTER(BodyOutStruct)]),
+        'shl_body_dev': (i32, [vp, vp, vp, vp, u64, C.POINTER(ParseOutStruct), C.POINTER(FrameOutStruct), C.POINTER(BodyOutStruct)]),
         'shl_chunk_header_batch': (i32, [vp, vp, u64, vp, vp, u64, vp, vp, vp]),
         'shl_parse_dev': (i32, [vp, vp, vp, vp, u64, C.POINTER(ParseOutStruct)]),
         'shl_frame_dev': (i32, [vp, vp, vp, vp, u64, vp, vp, vp, C.POINTER(FrameOutStruct)]),

@@ -101,6 +101,24 @@ class FrameOut(object):
         return s
 
 
+class BodyOut(object):
+    def __init__(self, n, body_cap, alloc=_np_alloc):
+        self.n, self.body_cap = int(n), int(body_cap)
+        self.body_off, self.body_len = alloc(n, np.uint64), alloc(n, np.uint64)
+        self.body = alloc(body_cap, np.uint8)
+        self.body_used = alloc(1, np.uint64)
+
+    def struct(self):
+        s = N.BodyOutStruct()
+        s.body_off, s.body_len = self.body_off.ctypes.data, self.body_len.ctypes.data
+        s.body, s.body_cap, s.body_used = self.body.ctypes.data, self.body_cap, self.body_used.ctypes.data
+        return s
+
+    def get(self, i):
+        o = int(self.body_off[i])
+        return self.body[o:o + int(self.body_len[i])].tobytes()
+
+
 class PlaceOut(object):
     def __init__(self, n, n_nodes=0, alloc=_np_alloc, want_md5=True):
         self.n = int(n)

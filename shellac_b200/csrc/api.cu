@@ -43,6 +43,7 @@ struct shl_ctx {
     std::vector<uint32_t> ring_values, ring_nodes;
     uint32_t n_points = 0, n_hosts = 0;
     uint64_t* d_hist = nullptr; uint32_t hist_cap = 0;
+    uint8_t* d_body = nullptr; uint64_t* d_body_off = nullptr; uint64_t* d_body_len = nullptr;   // body gather (lazy)
     int force_scalar = 0;
     uint64_t launches = 0;
     // pipelined host-buffer path: chunks round-robin over these streams so H2D, kernel and D2H overlap
@@ -199,6 +200,7 @@ void shl_ctx_destroy(shl_ctx* ctx) {
     cudaFree(ctx->d_ch_len); cudaFree(ctx->d_ch_size); cudaFree(ctx->d_ch_ok);
     cudaFree(ctx->d_counters); cudaFreeHost(ctx->h_counters);
     cudaFree(ctx->d_ring_values); cudaFree(ctx->d_ring_nodes); cudaFree(ctx->d_ring_dir); cudaFree(ctx->d_hist);
+    cudaFree(ctx->d_body); cudaFree(ctx->d_body_off); cudaFree(ctx->d_body_len);
     for (auto& e : ctx->ev) cudaEventDestroy(e);
     for (auto& st : ctx->pipe) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
     cudaEventDestroy(ctx->ev_fork);
@@ -614,6 +616,47 @@ int shl_frame_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, co
         if (used > d.chunk_cap || (out->chunk && used > out->chunk_cap))
             return fail(ctx, SHL_ERR_CAPACITY, "chunk record arena overflowed: raise max_records / chunk_cap");
     }
+    return SHL_OK;
+}
+
+int shl_body_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_off, const uint32_t* d_len, uint64_t n,
+                 const shl_parse_out* p, const shl_frame_out* f, const shl_body_out* d_out) {
+    if (!ctx || !d_arena || !d_off || !d_len || !p || !f || !d_out) return fail(ctx, SHL_ERR_ARG, "null pointer");
+    if (n == 0) return SHL_OK;
+    shl::BodyArgs a{};
+    a.arena = d_arena; a.off = d_off; a.len = d_len; a.n = n;
+    a.status = p->status; a.first_line_len = p->first_line_len; a.headers_len = p->headers_len; a.content_len = p->content_len;
+    a.sp1 = p->sp1;
+    a.fstatus = f->fstatus; a.n_chunks = f->n_chunks; a.chunk_base = f->chunk_base; a.chunk = f->chunk; a.body_bytes = f->body_bytes;
+    a.out = *d_out;
+    shl::k_body_plan<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(a);
+    shl::k_body_copy<<<dim3((unsigned)n, shl::kBodySlices), 256, 0, ctx->stream>>>(a);
+    ctx->launches += 2;
+    CU(cudaGetLastError());
+    return SHL_OK;
+}
+
+int shl_body_batch(shl_ctx* ctx, uint64_t n, const shl_body_out* out) {
+    if (!ctx || !out) return fail(ctx, SHL_ERR_ARG, "null pointer");
+    if (n > ctx->max_msgs) return fail(ctx, SHL_ERR_ARG, "batch larger than the capacity given to shl_ctx_create");
+    CU(cudaSetDevice(ctx->device));
+    if (!ctx->d_body) {
+        CU(cudaMalloc(reinterpret_cast<void**>(&ctx->d_body), ctx->max_bytes + 16 * ctx->max_msgs + 64));
+        CU(dalloc(&ctx->d_body_off, ctx->max_msgs)); CU(dalloc(&ctx->d_body_len, ctx->max_msgs));
+    }
+    shl_body_out d{};
+    d.body_off = ctx->d_body_off; d.body_len = ctx->d_body_len; d.body = ctx->d_body;
+    d.body_cap = std::min<uint64_t>(ctx->max_bytes + 16 * ctx->max_msgs, out->body ? out->body_cap : ~0ull);
+    d.body_used = ctx->d_counters + 1;                  // the frame pass is done with its counter
+    CU(cudaMemsetAsync(ctx->d_counters + 1, 0, 8, ctx->stream));
+    if (int rc = shl_body_dev(ctx, ctx->d_arena, ctx->d_off, ctx->d_len, n, &ctx->dp, &ctx->df, &d)) return rc;
+    D2H(out->body_off, d.body_off, n * 8); D2H(out->body_len, d.body_len, n * 8);
+    CU(cudaMemcpyAsync(ctx->h_counters + 1, ctx->d_counters + 1, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    const uint64_t used = ctx->h_counters[1];
+    if (out->body_used) *out->body_used = used;
+    if (used > d.body_cap) return fail(ctx, SHL_ERR_CAPACITY, "body arena overflowed: raise body_cap");
+    if (out->body && used) CU(cudaMemcpyAsync(out->body, d.body, used, cudaMemcpyDeviceToHost, ctx->stream));
     return SHL_OK;
 }
 

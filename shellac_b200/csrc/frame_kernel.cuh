@@ -165,3 +165,122 @@ __global__ void __launch_bounds__(256) k_place(const PlaceArgs a) {
 }
 
 }  // namespace shl
+
+// ----------------------------------------------------------------------------------- N1: body gather
+// De-chunk / body extraction: what the reference accumulates with _parse_body as it walks a
+// message (HttpParser.py:213-214 for Content-Length bodies, :296-297 per chunk, :340-347).  The
+// framing kernels only emit spans; this one copies the bytes those spans select into one
+// contiguous, 16-byte-aligned body per message, so `body().read()` can be served from a single
+// slice.  Pure data movement: 2 x body_len algorithmic bytes, HBM-bound.  gzip inflate stays on
+// the host (zlib), as in the reference.
+namespace shl {
+
+struct BodyArgs {
+    const uint8_t* arena; const uint64_t* off; const uint32_t* len; uint64_t n;
+    const uint32_t* status; const uint32_t* first_line_len; const uint32_t* headers_len; const int64_t* content_len;
+    const uint32_t* sp1;                                            // method span end (GET / HEAD have no body call)
+    const uint32_t* fstatus; const uint32_t* n_chunks; const uint32_t* chunk_base; const shl_chunk_span* chunk;
+    const uint64_t* body_bytes;
+    shl_body_out out;
+};
+
+// Plan: body length of message i and its slot in the body arena (one atomic per message).
+__global__ void __launch_bounds__(128) k_body_plan(const BodyArgs a) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.n) return;
+    const uint32_t st = a.status[i];
+    uint64_t blen = 0;
+    const bool hdr_done = (st & SHL_F_HEADERS_COMPLETE) && (st & 0xffu) < 16u;
+    if (hdr_done) {
+        const uint8_t* m = a.arena + a.off[i];
+        const uint32_t s1 = a.sp1[i];
+        const bool no_body_call = (st & SHL_F_IS_REQUEST) && (st & SHL_F_FIRST_LINE_DONE) &&
+                                  ((s1 == 3u && ldb(m) == 'G' && ldb(m + 1) == 'E' && ldb(m + 2) == 'T') ||
+                                   (s1 == 4u && ldb(m) == 'H' && ldb(m + 1) == 'E' && ldb(m + 2) == 'A' && ldb(m + 3) == 'D'));
+        if (!no_body_call) {
+            if (st & SHL_F_CHUNKED) { if (a.fstatus[i] != 0xffu) blen = a.body_bytes[i]; }
+            else if ((st & SHL_F_MESSAGE_COMPLETE) && !(st & SHL_F_CLEN_WIDE)) {       // partial data stays buffered (:209)
+                const int64_t avail = (int64_t)a.len[i] - ((int64_t)a.first_line_len[i] + a.headers_len[i]);
+                const int64_t cl = a.content_len[i];
+                blen = (uint64_t)(cl >= 0 ? (cl < avail ? cl : avail) : (avail + cl > 0 ? avail + cl : 0));   // data[:cl]
+            }
+        }
+    }
+    uint64_t boff = 0;
+    if (blen) {
+        boff = atomicAdd(reinterpret_cast<unsigned long long*>(a.out.body_used), (unsigned long long)((blen + 15ull) & ~15ull));
+        if (boff + blen > a.out.body_cap) blen = 0;                 // arena full: caller sees body_used > body_cap
+    }
+    a.out.body_off[i] = boff; a.out.body_len[i] = blen;
+}
+
+// Block-cooperative copy of n bytes, any alignment on either side: 16-byte aligned stores, two
+// aligned 16-byte loads per store re-aligned with funnel shifts; scalar bytes at the two edges.
+__device__ __forceinline__ void block_copy(uint8_t* __restrict__ dst, const uint8_t* __restrict__ src, uint64_t n) {
+    const uint64_t head0 = (16u - (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15)) & 15u;
+    const uint64_t head = n < head0 ? n : head0;
+    if (threadIdx.x < head) dst[threadIdx.x] = ldb(src + threadIdx.x);
+    dst += head; src += head; n -= head;
+    const uint64_t nv = n >> 4;
+    const uint32_t s = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 15);
+    const uint4* sv = reinterpret_cast<const uint4*>(src - s);
+    uint4* dv = reinterpret_cast<uint4*>(dst);
+    if (s == 0) {
+        for (uint64_t v = threadIdx.x; v < nv; v += blockDim.x) dv[v] = __ldg(sv + v);
+    } else {
+        const int wsel = (int)(s >> 2), sh = (int)(s & 3) * 8;
+        for (uint64_t v = threadIdx.x; v < nv; v += blockDim.x) {
+            const uint4 a0 = __ldg(sv + v), a1 = __ldg(sv + v + 1);
+            const uint32_t w[9] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w, 0u};
+            uint32_t o[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                uint32_t lo = 0, hi = 0;
+#pragma unroll
+                for (int j = 0; j < 4; j++) if (wsel == j) { lo = w[j + k]; hi = w[j + k + 1]; }
+                o[k] = __funnelshift_r(lo, hi, sh);
+            }
+            dv[v] = make_uint4(o[0], o[1], o[2], o[3]);
+        }
+    }
+    const uint64_t done = nv << 4, tail = n - done;
+    if (threadIdx.x < tail) dst[done + threadIdx.x] = ldb(src + done + threadIdx.x);
+}
+
+// Blocks (i, s), s < kBodySlices, share message i: a body is cut into 32 KiB slices and block s
+// copies slices s, s + kBodySlices, ...  (bodies span 4 KiB - 1 MiB: one block per message would
+// leave the tail of the grid to a few blocks grinding through megabyte bodies alone).
+constexpr int kBodySlices = 8;
+constexpr uint64_t kBodySlice = 32768;
+
+__global__ void __launch_bounds__(256) k_body_copy(const BodyArgs a) {
+    const uint64_t i = blockIdx.x;
+    const uint64_t blen = a.out.body_len[i];
+    if ((uint64_t)blockIdx.y * kBodySlice >= blen) return;
+    const uint8_t* m = a.arena + a.off[i];
+    uint8_t* dst = a.out.body + a.out.body_off[i];
+    const uint32_t st = a.status[i];
+    if (st & SHL_F_CHUNKED) {
+        const shl_chunk_span* c = a.chunk + a.chunk_base[i];
+        const uint32_t nc = a.n_chunks[i];
+        uint32_t k = 0;
+        uint64_t at = 0;                                            // body offset of chunk k
+        for (uint64_t lo = (uint64_t)blockIdx.y * kBodySlice; lo < blen; lo += kBodySlices * kBodySlice) {
+            const uint64_t hi = min(blen, lo + kBodySlice);
+            while (k < nc && at + c[k].data_len <= lo) { at += c[k].data_len; k++; }
+            uint32_t kk = k; uint64_t aa = at;
+            while (kk < nc && aa < hi) {                            // chunks overlapping [lo, hi)
+                const uint64_t dl = c[kk].data_len;
+                const uint64_t b0 = max(aa, lo), b1 = min(aa + dl, hi);
+                block_copy(dst + b0, m + c[kk].data_off + (b0 - aa), b1 - b0);
+                aa += dl; kk++;
+            }
+        }
+    } else {
+        const uint8_t* src = m + a.first_line_len[i] + a.headers_len[i];
+        for (uint64_t lo = (uint64_t)blockIdx.y * kBodySlice; lo < blen; lo += kBodySlices * kBodySlice)
+            block_copy(dst + lo, src + lo, min(blen, lo + kBodySlice) - lo);
+    }
+}
+
+}  // namespace shl

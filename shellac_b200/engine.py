@@ -9,7 +9,7 @@ import ctypes as C
 import numpy as np
 
 from . import _native as N
-from .batch import Arena, FrameOut, ParseOut, PlaceOut
+from .batch import Arena, BodyOut, FrameOut, ParseOut, PlaceOut
 
 
 def _check(lib, ctx, rc, what):
@@ -154,6 +154,16 @@ class Engine(object):
         rc = self.lib.shl_place_batch(self.ctx, arena.data.ctypes.data, arena.nbytes, key_off.ctypes.data,
                                       key_len.ctypes.data, n, C.byref(s))
         _check(self.lib, self.ctx, rc, 'shl_place_batch')
+        if sync:
+            self.sync()
+        return out
+
+    def body(self, arena, body_cap=0, sync=True, out=None):
+        """Gather the bodies of the batch just parsed + framed on this engine (shl_body_batch)."""
+        cap = int(body_cap) if body_cap else arena.nbytes + 16 * arena.n + 64
+        out = out or BodyOut(arena.n, cap, alloc=self.pinned)
+        s = out.struct()
+        _check(self.lib, self.ctx, self.lib.shl_body_batch(self.ctx, arena.n, C.byref(s)), 'shl_body_batch')
         if sync:
             self.sync()
         return out

@@ -9,7 +9,7 @@ import subprocess
 import numpy as np
 
 from shellac_b200 import _native as N
-from shellac_b200.batch import Arena, FrameOut, MessageView, ParseOut, PlaceOut
+from shellac_b200.batch import Arena, BodyOut, FrameOut, MessageView, ParseOut, PlaceOut
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORC_SRC = os.path.join(ROOT, 'oracle', 'shl_oracle.c')
@@ -33,6 +33,7 @@ def oracle():
         vp, u64 = C.c_void_p, C.c_uint64
         L.orc_parse.argtypes = [vp, vp, vp, u64, C.POINTER(N.ParseOutStruct)]
         L.orc_frame.argtypes = [vp, vp, vp, u64, vp, vp, vp, C.POINTER(N.FrameOutStruct)]
+        L.orc_body.argtypes = [vp, vp, vp, u64, C.POINTER(N.ParseOutStruct), C.POINTER(N.FrameOutStruct), C.POINTER(N.BodyOutStruct)]
         L.orc_chunk_header.argtypes = [vp, vp, vp, u64, vp, vp, vp]
         L.orc_md5.argtypes = [vp, u64, vp]
         L.orc_ring_build.argtypes = [C.POINTER(C.c_char_p), vp, vp, C.c_uint32, C.c_int, vp, vp, C.c_uint32]
@@ -56,6 +57,14 @@ def orc_frame(arena, pout, chunk_cap=None):
     oracle().orc_frame(arena.data.ctypes.data, arena.off.ctypes.data, arena.len.ctypes.data, n,
                        pout.status.ctypes.data, pout.first_line_len.ctypes.data,
                        pout.headers_len.ctypes.data, C.byref(s))
+    return out
+
+
+def orc_body(arena, pout, fout):
+    out = BodyOut(arena.n, arena.nbytes + 16 * arena.n + 64)
+    ps, fs, bs = pout.struct(), fout.struct(), out.struct()
+    oracle().orc_body(arena.data.ctypes.data, arena.off.ctypes.data, arena.len.ctypes.data, arena.n,
+                      C.byref(ps), C.byref(fs), C.byref(bs))
     return out
 
 

@@ -303,6 +303,33 @@ def test_c3_responses_framing(eng):
         assert len(v.raw_body()) == (int(gf.body_bytes[i]) if v.chunked() else v.content_len())
 
 
+def test_body_gather_matches_oracle(eng, golden):
+    """N1: the de-chunk / body gather (HttpParser._parse_body) against the oracle, byte for byte,
+    on the reference corpus (every alignment) and on config-3-shaped responses."""
+    rng = np.random.default_rng(20130731)
+    big = _response_corpus(rng, 40, lo=2000, hi=300000)
+    big += [m[:int(rng.integers(1, len(m)))] for m in big[:12]]
+    for name, msgs in (('golden', [w['msg'] for w in golden['whole']]), ('c3', big)):
+        ar = scatter_pack(eng, msgs, rng)
+        g = eng.parse(ar)
+        gf = eng.frame(ar, g, reuse_arena=True)
+        gb = eng.body(ar)
+        o = O.orc_parse(ar)
+        of = O.orc_frame(ar, o)
+        ob = O.orc_body(ar, o, of)
+        n = ar.n
+        assert (gb.body_len[:n] == ob.body_len[:n]).all(), name
+        assert int(gb.body_used[0]) == int(ob.body_used[0]), name
+        assert (gb.body_off[:n] % 16 == 0).all()
+        for i in range(n):
+            assert gb.get(i) == ob.get(i), (name, i, ar.message(i)[:120])
+        # bodies do not overlap
+        nz = gb.body_len[:n] > 0
+        order = np.argsort(gb.body_off[:n][nz])
+        b, l = gb.body_off[:n][nz][order].astype(np.int64), gb.body_len[:n][nz][order].astype(np.int64)
+        assert (b[1:] >= b[:-1] + l[:-1]).all(), name
+
+
 def test_chunk_header_primitive(eng):
     cases = [b'A;ext=foo\r\nAAAA', b'\r\n8;ext="foo"\r\nB', b'0\r\n\r\n', b'zz\r\n', b'0x1f\r\n', b'5', b' 5\r\n', b'',
              b'ffffffffffffffffffff\r\n', b'1;a=b;c=d\r\n', b'1;a="b\r\n', b'1;a=b"\r\n', b'1;a=""\r\n', b'\r\n\r\n5\r\n']

@@ -145,3 +145,21 @@ def test_py_port_placement_matches_golden(placement_golden):
         assert len(values) == r['n_points']
         got = [py_port.place(values, nodes, len(r['hosts']), k.encode('latin-1')) for k in placement_golden['keys']]
         assert got == r['node'], name
+
+
+def test_oracle_body_gather_matches_reference_bodies(golden):
+    """orc_body == what the reference's body() holds (identity content-coding cases)."""
+    msgs = [w['msg'] for w in golden['whole']]
+    ar = Arena.pack(msgs)
+    po = O.orc_parse(ar)
+    fo = O.orc_frame(ar, po)
+    bo = O.orc_body(ar, po, fo)
+    for i, w in enumerate(golden['whole']):
+        if 'gzip' in w['obs']['headers'].get('content-encoding', ''):
+            continue
+        if w['obs']['exc'] and w['obs']['headers_complete'] is False:
+            continue
+        v = MessageView(ar.message(i), po, i, fo)
+        assert bo.get(i) == v.raw_body(), w['id']
+        if not w['obs']['exc']:
+            assert bo.get(i).decode('latin-1') == w['obs']['body'], w['id']

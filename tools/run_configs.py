@@ -91,10 +91,27 @@ def c3(eng):
         eng.parse(ar, out=pout, sync=False)
         eng.frame(ar, pout, reuse_arena=True, out=fout, sync=True)
         e.append(time.perf_counter() - t0)
+    # N1: body gather on the resident batch
+    bstruct = N.BodyOutStruct()
+    d_boff, d_blen, d_body, d_bused = db._alloc(n * 8), db._alloc(n * 8), db._alloc(pos + 16 * n + 64), db._alloc(8)
+    bstruct.body_off, bstruct.body_len, bstruct.body, bstruct.body_cap, bstruct.body_used = d_boff, d_blen, d_body, pos + 16 * n, d_bused
+    bt = []
+    for it in range(8):
+        eng.memset(d_bused, 0, 8)
+        eng.event(3)
+        assert lib.shl_body_dev(ctx, db.d_arena, db.d_off, db.d_len, n, C.byref(ps), C.byref(fs), C.byref(bstruct)) == 0
+        eng.event(4)
+        eng.sync()
+        if it >= 3:
+            bt.append(eng.elapsed_ms(3, 4))
+    blen = db.fetch(d_blen, np.uint64, n)
+    assert int(blen.sum()) == body_total
+    bm = float(np.mean(bt))
     pm, fm = float(t[:, 0].mean()), float(t[:, 1].mean())
     return {'config': 3, 'responses': n, 'arena_gb': pos / 1e9, 'chunked': n // 2, 'chunks': n_chunks,
             'parse_ms': pm, 'frame_ms': fm, 'responses_per_s_resident': n / ((pm + fm) / 1e3),
             'chunks_per_s': n_chunks / (fm / 1e3), 'body_gb_s_skipped_by_arithmetic': pos / ((pm + fm) / 1e3) / 1e9,
+            'body_gather_ms': bm, 'body_gather_gb_s_algorithmic_2x': 2 * body_total / (bm / 1e3) / 1e9, 'body_bytes': body_total,
             'e2e_ms_best': min(e) * 1e3, 'e2e_responses_per_s': n / min(e), 'e2e_gb_s': pos / min(e) / 1e9,
             'note': 'framing is a pointer chase over chunk headers: latency-bound, bodies are never read; e2e is the H2D of the bodies'}
 
