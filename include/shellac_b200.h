@@ -216,6 +216,14 @@ int  shl_chunk_header_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_b
  * shl_body_batch works on the batch whose shl_parse_batch + shl_frame_batch results are still
  * resident on this ctx (call it right after them, same n).                                       */
 int  shl_body_batch(shl_ctx* ctx, uint64_t n, const shl_body_out* out);
+/* Group the requests of a placed batch by node: what pylibmc does behind get/set before it
+ * talks to each memcached node (Server.py:335, 432).  start[k] .. start[k+1] index the requests
+ * of node k in order[] (start has n_hosts + 1 entries; requests without a node are left out; the
+ * order inside a node is arbitrary).  shl_group_batch works on the batch whose shl_route_batch /
+ * shl_place_batch results (with a histogram) are still resident on this ctx.                     */
+int  shl_group_batch(shl_ctx* ctx, uint64_t n, uint32_t* start, uint32_t* order);
+int  shl_group_dev(shl_ctx* ctx, const uint32_t* d_node, uint64_t n, uint32_t n_hosts, const uint64_t* d_hist,
+                   uint32_t* d_start, uint32_t* d_cursor, uint32_t* d_order);
 /* In every *_batch call `arena` may be NULL: the bytes uploaded by the previous *_batch call on
  * this ctx are reused (parse, then frame the same arena, costs one H2D copy).                    */
 

@@ -121,6 +121,8 @@ def lib():
         'shl_route_batch': (i32, [vp, vp, u64, vp, vp, u64, C.POINTER(ParseOutStruct), C.POINTER(PlaceOutStruct)]),
         'shl_body_batch': (i32, [vp, u64, C.POINTER(BodyOutStruct)]),
         'shl_body_dev': (i32, [vp, vp, vp, vp, u64, C.POINTER(ParseOutStruct), C.POINTER(FrameOutStruct), C.POINTER(BodyOutStruct)]),
+        'shl_group_batch': (i32, [vp, u64, vp, vp]),
+        'shl_group_dev': (i32, [vp, vp, u64, C.c_uint32, vp, vp, vp, vp]),
         'shl_chunk_header_batch': (i32, [vp, vp, u64, vp, vp, u64, vp, vp, vp]),
         'shl_parse_dev': (i32, [vp, vp, vp, vp, u64, C.POINTER(ParseOutStruct)]),
         'shl_frame_dev': (i32, [vp, vp, vp, vp, u64, vp, vp, vp, C.POINTER(FrameOutStruct)]),

@@ -43,6 +43,7 @@ struct shl_ctx {
     std::vector<uint32_t> ring_values, ring_nodes;
     uint32_t n_points = 0, n_hosts = 0;
     uint64_t* d_hist = nullptr; uint32_t hist_cap = 0;
+    uint32_t* d_gstart = nullptr; uint32_t* d_gcursor = nullptr; uint32_t* d_gorder = nullptr; uint32_t gcap = 0;   // grouping (lazy)
     uint8_t* d_body = nullptr; uint64_t* d_body_off = nullptr; uint64_t* d_body_len = nullptr;   // body gather (lazy)
     int force_scalar = 0;
     uint64_t launches = 0;
@@ -201,6 +202,7 @@ void shl_ctx_destroy(shl_ctx* ctx) {
     cudaFree(ctx->d_counters); cudaFreeHost(ctx->h_counters);
     cudaFree(ctx->d_ring_values); cudaFree(ctx->d_ring_nodes); cudaFree(ctx->d_ring_dir); cudaFree(ctx->d_hist);
     cudaFree(ctx->d_body); cudaFree(ctx->d_body_off); cudaFree(ctx->d_body_len);
+    cudaFree(ctx->d_gstart); cudaFree(ctx->d_gcursor); cudaFree(ctx->d_gorder);
     for (auto& e : ctx->ev) cudaEventDestroy(e);
     for (auto& st : ctx->pipe) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
     cudaEventDestroy(ctx->ev_fork);
@@ -657,6 +659,33 @@ int shl_body_batch(shl_ctx* ctx, uint64_t n, const shl_body_out* out) {
     if (out->body_used) *out->body_used = used;
     if (used > d.body_cap) return fail(ctx, SHL_ERR_CAPACITY, "body arena overflowed: raise body_cap");
     if (out->body && used) CU(cudaMemcpyAsync(out->body, d.body, used, cudaMemcpyDeviceToHost, ctx->stream));
+    return SHL_OK;
+}
+
+int shl_group_dev(shl_ctx* ctx, const uint32_t* d_node, uint64_t n, uint32_t n_hosts, const uint64_t* d_hist,
+                  uint32_t* d_start, uint32_t* d_cursor, uint32_t* d_order) {
+    if (!ctx || !d_node || !d_hist || !d_start || !d_cursor || !d_order || n_hosts == 0) return fail(ctx, SHL_ERR_ARG, "null pointer");
+    shl::k_group_scan<<<1, 1024, 0, ctx->stream>>>(d_hist, n_hosts, d_start, d_cursor);
+    if (n) shl::k_group_scatter<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(d_node, n, n_hosts, d_cursor, d_order);
+    ctx->launches += 2;
+    CU(cudaGetLastError());
+    return SHL_OK;
+}
+
+int shl_group_batch(shl_ctx* ctx, uint64_t n, uint32_t* start, uint32_t* order) {
+    if (!ctx || !start || !order) return fail(ctx, SHL_ERR_ARG, "null pointer");
+    if (!ctx->d_ring_values) return fail(ctx, SHL_ERR_NO_RING, "shl_ring_build() has not been called");
+    if (n > ctx->max_msgs) return fail(ctx, SHL_ERR_ARG, "batch larger than the capacity given to shl_ctx_create");
+    CU(cudaSetDevice(ctx->device));
+    if (!ctx->d_gorder) CU(dalloc(&ctx->d_gorder, ctx->max_msgs));
+    if (ctx->gcap < ctx->n_hosts + 1) {
+        cudaFree(ctx->d_gstart); cudaFree(ctx->d_gcursor); ctx->d_gstart = ctx->d_gcursor = nullptr;
+        CU(dalloc(&ctx->d_gstart, ctx->n_hosts + 1)); CU(dalloc(&ctx->d_gcursor, ctx->n_hosts + 1));
+        ctx->gcap = ctx->n_hosts + 1;
+    }
+    if (int rc = shl_group_dev(ctx, ctx->dq.node, n, ctx->n_hosts, ctx->d_hist, ctx->d_gstart, ctx->d_gcursor, ctx->d_gorder)) return rc;
+    CU(cudaMemcpyAsync(start, ctx->d_gstart, (size_t)(ctx->n_hosts + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaMemcpyAsync(order, ctx->d_gorder, n * 4, cudaMemcpyDeviceToHost, ctx->stream));   // only start[n_hosts] entries are meaningful
     return SHL_OK;
 }
 

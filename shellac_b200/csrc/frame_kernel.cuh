@@ -284,3 +284,61 @@ __global__ void __launch_bounds__(256) k_body_copy(const BodyArgs a) {
 }
 
 }  // namespace shl
+
+// ----------------------------------------------------------------------------------- N3: group by node
+// After placement the cache client talks to each memcached node separately (pylibmc does this
+// behind Server.py:335 / :432).  These two kernels turn node[n] into a permutation grouped by
+// node: start[k] .. start[k+1] index the requests of node k in order[] (unplaced ones, node ==
+// 0xffffffff, are left out; order inside a node is arbitrary).
+namespace shl {
+
+// one block: exclusive scan of the per-node histogram into start[0..n_hosts], cursor[k] = start[k]
+__global__ void __launch_bounds__(1024) k_group_scan(const uint64_t* __restrict__ hist, uint32_t n_hosts,
+                                                     uint32_t* __restrict__ start, uint32_t* __restrict__ cursor) {
+    __shared__ uint32_t warp_sum[32];
+    __shared__ uint32_t carry;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < n_hosts; base += blockDim.x) {
+        const uint32_t k = base + threadIdx.x;
+        const uint32_t v = k < n_hosts ? (uint32_t)hist[k] : 0u;
+        uint32_t inc = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(SHL_FULL, inc, d); if (lane >= d) inc += t; }
+        if (lane == 31) warp_sum[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            uint32_t w = warp_sum[lane], wi = w;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(SHL_FULL, wi, d); if (lane >= d) wi += t; }
+            warp_sum[lane] = wi - w;                               // exclusive over warps
+        }
+        __syncthreads();
+        const uint32_t excl = carry + warp_sum[warp] + inc - v;
+        if (k < n_hosts) { start[k] = excl; cursor[k] = excl; }
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1) carry = excl + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) start[n_hosts] = carry;
+}
+
+// thread per request; lanes of a warp that hit the same node share one atomic (__match_any_sync)
+__global__ void __launch_bounds__(256) k_group_scatter(const uint32_t* __restrict__ node, uint64_t n, uint32_t n_hosts,
+                                                       uint32_t* __restrict__ cursor, uint32_t* __restrict__ order) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const uint32_t nd = i < n ? node[i] : 0xffffffffu;
+    const bool placed = nd < n_hosts;
+    const uint32_t key = placed ? nd : 0xffffffffu;
+    const uint32_t peers = __match_any_sync(SHL_FULL, key);
+    if (!placed) return;
+    const int leader = __ffs(peers) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(&cursor[nd], (uint32_t)__popc(peers));
+    base = __shfl_sync(peers, base, leader);
+    order[base + __popc(peers & ((1u << lane) - 1u))] = (uint32_t)i;
+}
+
+}  // namespace shl

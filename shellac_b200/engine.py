@@ -168,6 +168,14 @@ class Engine(object):
             self.sync()
         return out
 
+    def group(self, n):
+        """Requests of the batch just routed/placed (with a histogram), grouped by node:
+        (start[n_hosts + 1], order[n]); node k owns order[start[k]:start[k + 1]]."""
+        start, order = self.pinned(self.n_hosts + 1, np.uint32), self.pinned(n, np.uint32)
+        _check(self.lib, self.ctx, self.lib.shl_group_batch(self.ctx, n, start.ctypes.data, order.ctypes.data), 'shl_group_batch')
+        self.sync()
+        return start, order[:n]
+
     def chunk_header(self, arena):
         n = arena.n
         hl, sz, ok = self.pinned(n, np.int32), self.pinned(n, np.uint64), self.pinned(n, np.uint8)

@@ -399,6 +399,25 @@ def test_route_fused_matches_parse_then_place(eng, golden):
     assert (ks.node[:int(r.sum())] == qg.node[:n][r]).all()
 
 
+def test_group_by_node_after_route(eng, golden):
+    """N3: the per-node grouping pylibmc does behind get/set (Server.py:335,432)."""
+    for hosts in (['10.0.0.%d' % (i + 1) for i in range(16)], ['10.3.%d.%d' % (i // 250, i % 250 + 1) for i in range(1500)]):
+        eng.ring_build(hosts)
+        c2 = eng.corpus_host(20130725, 7000, 20000, 0)
+        msgs = [c2.message(i) for i in range(20000)] + [w['msg'] for w in golden['whole'][:1500]]
+        ar = eng.pack(msgs)
+        pg, qg = eng.route(ar)
+        start, order = eng.group(ar.n)
+        node = qg.node[:ar.n]
+        placed = node != 0xffffffff
+        assert int(start[len(hosts)]) == int(placed.sum()) and int(start[0]) == 0
+        assert (np.diff(start.astype(np.int64)) == np.bincount(node[placed], minlength=len(hosts))).all()
+        got = order[:int(start[len(hosts)])]
+        assert len(np.unique(got)) == len(got) and placed[got].all()
+        owner = np.repeat(np.arange(len(hosts)), np.diff(start.astype(np.int64)))
+        assert (node[got] == owner).all()
+
+
 def test_c2_full_size_properties(eng):
     """BASELINE config 2 at full size (1 M GETs, 16x100 ring): size-independent properties plus a
     full comparison with the oracle (the C oracle finishes 1 M messages in seconds)."""
