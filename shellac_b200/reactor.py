@@ -1,0 +1,139 @@
+"""Reactor batching shim: the caller-side change that lets a live,
+single-threaded epoll reactor use the batch path.
+
+The reference parses inside its read handlers, one `recv(4096)` at a time, one connection at a time
+(`Server._read_requests`, Server.py:302-377: `parsed = request.parse(data, len(data))` ...
+`key = request.url()` ... `self._mc.get(key)`).  With this shim the handlers only `feed(fd, data)`;
+once per epoll tick `tick()` packs every connection's pending bytes into ONE arena, makes ONE
+`route` call (tokenise + key + placement on the device) and hands back, per connection, the
+requests that completed, in arrival order, each with its cache key and memcached node.  Bytes of
+a request that is not complete yet stay queued for the next tick, exactly like the reference's
+parser keeps them in `_buf` (HttpParser.py:153,174,209); pipelined requests on one connection are
+peeled off in further rounds of the same tick (Server.py:320 `while len(data) != 0`).
+
+`router` is anything with `route(messages) -> (parse_out, place_out, frame_out_or_None)`;
+`EngineRouter` below is the real one.  There is no CPU path in this package.
+"""
+from . import _native as N
+from .batch import MessageView
+
+
+class Routed(object):
+    """One completed request: what Server._read_requests has in hand at Server.py:325-335."""
+    __slots__ = ('fd', 'view', 'key', 'node', 'error', 'raw')
+
+    def __init__(self, fd, view, key, node, error, raw):
+        self.fd, self.view, self.key, self.node, self.error, self.raw = fd, view, key, node, error, raw
+
+
+class EngineRouter(object):
+    """route() through an Engine: fused parse + key + placement, chunk framing when needed."""
+
+    def __init__(self, engine):
+        self.eng = engine
+
+    def route(self, messages):
+        eng = self.eng
+        mark = len(eng._pinned)
+        try:
+            ar = eng.pack(messages)
+            pout, qout = eng.route(ar)
+            fout = None
+            if ((pout.status[:ar.n] & N.F_CHUNKED) != 0).any():
+                fout = eng.frame(ar, pout, reuse_arena=True)
+                fout = _detach_frame(fout, ar.n)
+            return _detach_parse(pout, ar.n), _detach_place(qout, ar.n), fout
+        finally:
+            eng.release_pinned(mark)
+
+    def place_keys(self, keys):
+        eng = self.eng
+        mark = len(eng._pinned)
+        try:
+            out = eng.place(eng.pack(keys))
+            return out.node[:len(keys)].copy()
+        finally:
+            eng.release_pinned(mark)
+
+
+class _Bag(object):
+    pass
+
+
+def _detach_parse(p, n):
+    b = _Bag()
+    for name, _ in N.PARSE_FIELDS:
+        setattr(b, name, getattr(p, name)[:n].copy())
+    b.hdr = p.hdr.copy()
+    return b
+
+
+def _detach_frame(f, n):
+    b = _Bag()
+    for name, _ in N.FRAME_FIELDS:
+        setattr(b, name, getattr(f, name)[:n].copy())
+    b.chunk = f.chunk.copy()
+    return b
+
+
+def _detach_place(q, n):
+    b = _Bag()
+    b.node, b.hash = q.node[:n].copy(), q.hash[:n].copy()
+    return b
+
+
+class ReactorShim(object):
+    MAX_ROUNDS = 64          # pipelined requests peeled per connection per tick
+
+    def __init__(self, router):
+        self.router = router
+        self.pending = {}                  # fd -> bytearray of bytes not yet consumed
+
+    def feed(self, fd, data):
+        """Called from the read handler instead of request.parse(data, len(data))."""
+        if isinstance(data, str):
+            data = data.encode('latin-1')
+        self.pending.setdefault(fd, bytearray()).extend(data)
+
+    def close(self, fd):
+        self.pending.pop(fd, None)
+
+    def tick(self):
+        """One batch per round over every connection with pending bytes.  Returns a list of
+        Routed in (round, fd) order.  Connections whose next request is incomplete keep their
+        bytes; a request the reference would have raised on is returned with `.error` set and its
+        connection's bytes are dropped."""
+        done = []
+        live = [fd for fd, buf in self.pending.items() if len(buf)]
+        for _ in range(self.MAX_ROUNDS):
+            if not live:
+                break
+            msgs = [bytes(self.pending[fd]) for fd in live]
+            pout, qout, fout = self.router.route(msgs)
+            late_keys, late_items, again = [], [], []
+            for i, fd in enumerate(live):
+                v = MessageView(msgs[i], pout, i, fout)
+                exc = v.exception()
+                if exc is not None:
+                    done.append(Routed(fd, v, None, None, exc(N.CODE_NAMES.get(v.code, '?')), msgs[i]))
+                    self.pending[fd] = bytearray()
+                    continue
+                if not v.message_complete():
+                    continue                                   # wait for more bytes (next tick)
+                used = v.consumed()
+                raw = msgs[i][:used]
+                del self.pending[fd][:used]
+                key = v.url()
+                node = int(qout.node[i]) if key is not None else None
+                item = Routed(fd, v, key, node, None, raw)
+                if key is not None and node == 0xffffffff:     # completed by the chunk framer: place it now
+                    late_keys.append(key)
+                    late_items.append(item)
+                done.append(item)
+                if len(self.pending[fd]):
+                    again.append(fd)
+            if late_keys:
+                for item, nd in zip(late_items, self.router.place_keys(late_keys)):
+                    item.node = int(nd)
+            live = again
+        return done
