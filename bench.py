@@ -52,6 +52,7 @@ class ClockSampler(threading.Thread):
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.samples, self.reasons, self.stop_flag, self.max_mhz = index, [], set(), False, None
+        self.armed = threading.Event()      # NVML start-up costs milliseconds: do it BEFORE the barrier
         try:
             import pynvml
             pynvml.nvmlInit()
@@ -71,6 +72,7 @@ class ClockSampler(threading.Thread):
                  nv.nvmlClocksThrottleReasonSwThermalSlowdown: 'sw_thermal_slowdown',
                  nv.nvmlClocksThrottleReasonSwPowerCap: 'sw_power_cap',
                  nv.nvmlClocksThrottleReasonHwPowerBrakeSlowdown: 'hw_power_brake'}
+        self.armed.wait()
         while not self.stop_flag:
             try:
                 self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
@@ -80,10 +82,11 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(name)
             except Exception:       # noqa: BLE001
                 pass
-            time.sleep(0.02)
+            time.sleep(0.002)
 
     def result(self):
         self.stop_flag = True
+        self.armed.set()
         if not self.samples:
             return {'sm_mhz': None, 'sm_max_mhz': self.max_mhz, 'reasons': sorted(self.reasons)}
         return {'sm_mhz': float(np.median(self.samples)), 'sm_max_mhz': self.max_mhz,
@@ -260,25 +263,61 @@ def run_ours(args):
     qs.md5, qs.hash, qs.node = eng.dev_alloc(16 * n), eng.dev_alloc(4 * n), eng.dev_alloc(4 * n)
     n_stat = len(HOSTS) + N.N_CODES
     if world > 1:
-        stats = torch.zeros(n_stat, dtype=torch.int64, device='cuda:%d' % local)   # [hist | code counts]
-        d_stats = stats.data_ptr()
         from shellac_b200 import dist as D
+        # two stats buffers [hist | code counts]: the all-reduce of step k runs on its own stream while
+        # the kernel of step k+1 is already scanning (collective overlapped with compute)
+        stats2 = [torch.zeros(n_stat, dtype=torch.int64, device='cuda:%d' % local) for _ in range(2)]
         ext = D.external_stream(eng, local)
+        comm = torch.cuda.Stream(device='cuda:%d' % local)
+        ev_ready = [torch.cuda.Event() for _ in range(2)]       # stats[k] written by the kernel
+        ev_free = [torch.cuda.Event() for _ in range(2)]        # stats[k] reduced, may be overwritten
+        for e in ev_free:
+            e.record(comm)
+        d_stats_list = [t.data_ptr() for t in stats2]
     else:
-        d_stats = eng.dev_alloc(n_stat * 8)
-    qs.hist = d_stats
+        d_stats_list = [eng.dev_alloc(n_stat * 8)]
     d_codes = lib.shl_code_hist_dev(ctx)
+    # The path has no exchange step (requests are independent): ranks only share the per-node and
+    # per-outcome COUNTERS.  They accumulate on the device over `--stats-every` steps (0 = the whole
+    # timed region) and are then all-reduced on a side stream while the next kernel already runs.
+    st = {'k': 0, 'since': 0, 'fresh': True}
+
+    def reduce_stats():
+        k = st['k']
+        lib.shl_memcpy_d2d(ctx, d_stats_list[k] + len(HOSTS) * 8, d_codes, N.N_CODES * 8)
+        st['last'] = k
+        st['since'] = 0
+        st['fresh'] = True
+        if world > 1:
+            ev_ready[k].record(ext)
+            comm.wait_event(ev_ready[k])
+            with torch.cuda.stream(comm):
+                D.allreduce_stats(stats2[k])
+                ev_free[k].record(comm)
+            st['k'] = (k + 1) % len(d_stats_list)
 
     def step_resident():
+        k = st['k']
+        if st['fresh']:
+            if world > 1:
+                ext.wait_event(ev_free[k])
+            eng.memset(d_stats_list[k], 0, n_stat * 8)
+            eng.memset(d_codes, 0, N.N_CODES * 8)
+            st['fresh'] = False
+        qs.hist = d_stats_list[k]
         eng.memset(d_used, 0, 8)
-        eng.memset(d_stats, 0, n_stat * 8)
-        eng.memset(d_codes, 0, N.N_CODES * 8)
         rc = lib.shl_route_dev(ctx, d_arena, d_off, d_len, n, C.byref(ps), C.byref(qs))
         assert rc == 0, lib.shl_last_error(ctx)
-        lib.shl_memcpy_d2d(ctx, d_stats + len(HOSTS) * 8, d_codes, N.N_CODES * 8)
-        if world > 1:
-            with torch.cuda.stream(ext):
-                D.allreduce_stats(stats)
+        st['since'] += 1
+        if args.stats_every and st['since'] >= args.stats_every:
+            reduce_stats()
+
+    def flush_resident():
+        if st['since']:
+            reduce_stats()
+        if world > 1:                       # the timed region ends when the last all-reduce has finished
+            for e in ev_free:
+                ext.wait_event(e)
 
     def barrier():
         eng.sync()
@@ -287,16 +326,21 @@ def run_ours(args):
             dist.barrier()
             torch.cuda.synchronize()
 
-    def timed(fn, steps, warmup):
+    def timed(fn, steps, warmup, flush=None):
         for _ in range(warmup):
             fn()
-        barrier()
+        if flush:
+            flush()
         sampler = ClockSampler(local)
         sampler.start()
+        barrier()
+        sampler.armed.set()
         l0 = eng.launches()
         eng.event(0)
         for _ in range(steps):
             fn()
+        if flush:
+            flush()
         eng.event(1)
         barrier()
         ms = eng.elapsed_ms(0, 1)
@@ -307,25 +351,28 @@ def run_ours(args):
             ms = float(t.item())
         return ms, clocks, eng.launches() - l0
 
-    ms, clocks, launches = timed(step_resident, args.steps, args.warmup)
+    ms, clocks, launches = timed(step_resident, args.steps, args.warmup, flush_resident)
     # kernel-only duration for the roofline: events around the kernel alone, averaged over the steps
     eng.sync()
     kms = []
     for _ in range(args.steps):
         eng.memset(d_used, 0, 8)
-        eng.memset(d_stats, 0, n_stat * 8)
+        qs.hist = d_stats_list[0]
         eng.event(2)
         lib.shl_route_dev(ctx, d_arena, d_off, d_len, n, C.byref(ps), C.byref(qs))
         eng.event(3)
         eng.sync()
         kms.append(eng.elapsed_ms(2, 3))
     k_ms = float(np.mean(kms))
+    log('[rank %d] kernel alone %.4f ms, step %.4f ms (max over ranks)' % (rank, k_ms, ms / args.steps))
 
     # ---- check the resident result (outside the timed region): histogram adds up
+    st['fresh'] = True
     step_resident()
+    flush_resident()
     barrier()
     hs = np.zeros(n_stat, np.uint64)
-    eng.d2h(hs, d_stats); eng.sync()
+    eng.d2h(hs, d_stats_list[st['last']]); eng.sync()
     total_hdrs = np.zeros(1, np.uint64)
     eng.d2h(total_hdrs, d_used); eng.sync()
     expect = n * (world if world > 1 else 1)
@@ -367,7 +414,8 @@ def run_ours(args):
         'vs_baseline': None, 'dtype': 'u8', 'data': 'synthetic',
         'config': {'workload': WORKLOAD, 'batch_per_gpu': n, 'mean_request_bytes': nbytes / n,
                    'mean_header_lines': n_hdr / n, 'ring': '16x100 ketama/MD5 (libmemcached 0.44 "ketama": True)',
-                   'parallelism': 'dp%d (batch-sharded, all-reduce of %d int64 counters per step)' % (world, n_stat),
+                   'parallelism': 'dp%d (batch-sharded, no data-path collective; %d int64 counters all-reduced %s)' % (
+                       world, n_stat, 'every %d steps' % args.stats_every if args.stats_every else 'once per timed region'),
                    'l2': 'inputs (%.0f MB per GPU) exceed the 126 MB L2; no flush needed' % (nbytes / 1e6)},
         'header_gb_s': nbytes * world * args.steps / (ms / 1e3) / 1e9,
         'clocks': clocks, 'gpu_launches': launches,
@@ -413,6 +461,8 @@ def main():
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--batch', type=int, default=BATCH)
+    ap.add_argument('--stats-every', type=int, default=0,
+                    help='all-reduce the per-node / per-outcome counters every S steps (0: once, at the end of the timed steps)')
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
