@@ -238,6 +238,11 @@ def run_ours(args):
         dist.init_process_group('nccl', device_id=torch.device('cuda', local))
         dist.barrier()
     n = args.batch
+    numa = None
+    if not os.environ.get('SHL_NO_BIND'):
+        from shellac_b200.hostmem import bind_near_gpu
+        numa = bind_near_gpu(local)          # before any pinned arena is allocated
+    log('[rank %d] numa binding: %r, %d cpus allowed' % (rank, numa, len(os.sched_getaffinity(0))))
     eng = Engine(device=local, max_msgs=n, max_bytes=n * 640, max_records=n * 24)
     lib, ctx = eng.lib, eng.ctx
     eng.ring_build(HOSTS)
@@ -424,6 +429,7 @@ def run_ours(args):
                 'pcie_gb_s_h2d': h2d * args.steps / (e_ms / 1e3) / 1e9, 'ms_per_step': e_ms / args.steps,
                 'pcie_probe': pcie, 'frac_of_pcie_h2d_roofline': (h2d * args.steps / (e_ms / 1e3) / 1e9) / pcie['h2d_gb_s'],
                 'note': 'chunked over 4 streams: H2D, kernel and D2H of different chunks overlap; bound by the H2D link',
+                'host_numa': 'process bound to NUMA node %d (%d cpus) of its GPU' % numa if numa else 'unbound',
                 'clocks': e_clocks},
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
                      'traffic': ncu_traffic(), 'kernel': 'shl::k_route<true>', 'kernel_ms': k_ms,

@@ -151,6 +151,9 @@ typedef struct shl_ctx shl_ctx;
  * device buffers, the stream and the ring.
  * ---------------------------------------------------------------------------------------- */
 int  shl_device_count(void);
+/* "0000:1b:00.0"-style PCI address of a device (len >= 13), so that the host side can place its
+ * pinned arenas on the GPU's NUMA node (shellac_b200/hostmem.py).  No reference counterpart. */
+int  shl_device_pci_bus_id(int device, char* buf, int len);
 int  shl_ctx_create(int device, uint64_t max_msgs, uint64_t max_bytes, uint64_t max_records, shl_ctx** out);
 void shl_ctx_destroy(shl_ctx* ctx);
 const char* shl_last_error(shl_ctx* ctx);           /* ctx may be NULL: last error of ctx creation */

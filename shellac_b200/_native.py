@@ -97,6 +97,7 @@ def lib():
     vp, u64, i32 = C.c_void_p, C.c_uint64, C.c_int
     sig = {
         'shl_device_count': (i32, []),
+        'shl_device_pci_bus_id': (i32, [i32, C.c_char_p, i32]),
         'shl_ctx_create': (i32, [i32, u64, u64, u64, C.POINTER(vp)]),
         'shl_ctx_destroy': (None, [vp]),
         'shl_last_error': (C.c_char_p, [vp]),

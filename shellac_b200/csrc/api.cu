@@ -140,6 +140,11 @@ int shl_device_count(void) {
     return n;
 }
 
+int shl_device_pci_bus_id(int device, char* buf, int len) {
+    if (!buf || len < 13) return -1;
+    return cudaDeviceGetPCIBusId(buf, len, device) == cudaSuccess ? 0 : -2;
+}
+
 const char* shl_last_error(shl_ctx* ctx) { return ctx ? ctx->err.c_str() : g_last_error.c_str(); }
 
 int shl_ctx_create(int device, uint64_t max_msgs, uint64_t max_bytes, uint64_t max_records, shl_ctx** out) {
