@@ -41,6 +41,15 @@ namespace shl {
 #ifndef SHL_OPT_MINBLOCKS
 #define SHL_OPT_MINBLOCKS 8
 #endif
+#ifndef SHL_OPT_EVFIRST
+#define SHL_OPT_EVFIRST 1
+#endif
+#ifndef SHL_OPT_UNROLL2
+#define SHL_OPT_UNROLL2 0
+#endif
+#ifndef SHL_OPT_STEP16
+#define SHL_OPT_STEP16 0
+#endif
 #ifndef SHL_OPT_BATCH
 #define SHL_OPT_BATCH 2
 #endif
@@ -199,17 +208,8 @@ __device__ __forceinline__ void finalize_headers(const uint8_t* m, int L, int bo
     } else status |= SHL_S_INCOMPLETE_BODY;
 }
 
-// unaligned little-endian 32-bit load (may touch up to 3 bytes past p+4, inside the arena padding)
-__device__ __forceinline__ uint32_t ld32u(const uint8_t* p) {
-    const uint32_t* a = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(p) & ~(uintptr_t)3);
-    const int sh = (int)(reinterpret_cast<uintptr_t>(p) & 3) * 8;
-    const uint32_t lo = __ldg(a);
-    const uint32_t hi = sh ? __ldg(a + 1) : 0u;
-    return __funnelshift_r(lo, hi, sh);
-}
-
 // ----------------------------------------------------------------------------------- scan: one message, one lane
-struct LaneScan { int idx, T, sp1, sp2; uint32_t n_c, n_s, s_skip, first_bad, bad_cnt; bool ovf; };
+struct LaneScan { int idx, T, sp1, sp2; uint32_t n_c, n_s, s_skip; bool ovf, bad; };
 
 // cr[k * 32] / sp[k * 32]: this lane's slots of the warp's position lists (u16, lane-interleaved).
 // 0xFFFF in each 16-bit half of x that equals the matching half of pat.  The halves are compared
@@ -220,74 +220,157 @@ __device__ __forceinline__ uint32_t eq16x2(uint32_t x, uint32_t pat) {
     return __heq2_mask(*reinterpret_cast<const __half2*>(&x), *reinterpret_cast<const __half2*>(&pat));
 }
 
-// Event bits of one 32-bit word w (nx = the word that follows it in memory), position-ordered:
-// bit 2j = ": " starts at byte j, bit 2j+1 = CRLF starts at byte j.
-__device__ __forceinline__ uint32_t pair_events(uint32_t w, uint32_t nx) {
-    const uint32_t sh = __funnelshift_r(w, nx, 8);                     // bytes 1..4: the odd alignment
-    const uint32_t fc = __byte_perm(eq16x2(w, 0x0A0D0A0Du), eq16x2(sh, 0x0A0D0A0Du), 0x6240);   // 0xFF per byte that starts a CRLF
-    const uint32_t fs = __byte_perm(eq16x2(w, 0x203A203Au), eq16x2(sh, 0x203A203Au), 0x6240);   // ... that starts a ": "
+// Event bits of one 32-bit word w (pv = the word BEFORE it in memory), position-ordered, for the
+// four byte pairs that END inside w: bit 2j = a ": " starts at byte j-1 of w, bit 2j+1 = a CRLF
+// starts there (j = 0 is the pair that straddles pv and w).  Looking backwards means the scan
+// carries one word and never loads ahead of the byte it is classifying.
+__device__ __forceinline__ uint32_t pair_events(uint32_t pv, uint32_t w) {
+    const uint32_t sh = __funnelshift_r(pv, w, 24);                    // bytes -1..2: the odd alignment
+    const uint32_t fc = __byte_perm(eq16x2(w, 0x0A0D0A0Du), eq16x2(sh, 0x0A0D0A0Du), 0x2604);   // 0xFF per pair that is a CRLF
+    const uint32_t fs = __byte_perm(eq16x2(w, 0x203A203Au), eq16x2(sh, 0x203A203Au), 0x2604);   // ... that is a ": "
     return __umulhi((fc & 0x80808080u) | (fs & 0x40404040u), 0x04104100u);   // [s0 c0 s1 c1 s2 c2 s3 c3] + stray bits above bit 7
 }
 
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
 __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
 
+// Running state of one lane's scan.  Events are only LISTED here (positions of the CR of every
+// CRLF, of the ':' of every ": "); which separator belongs to which line is worked out afterwards
+// from the positions (count_lines), when the lanes are converged again.
+struct ScanState {
+    int T, last_cr, sp1, sp2;
+    uint32_t n_c, n_s;
+    uint32_t s_prev, s_skip, bad;      // ": " listed before the last CRLF / inside the first line; some line did not hold exactly one
+};
+
+// One 16-byte vector v at message position p (byte 0 of v), c = the word before it.
+__device__ __forceinline__ void scan_step(const uint4& v, const uint32_t c, const int p, const int L,
+                                          uint16_t* cr, uint16_t* sp, const SwarK& K, ScanState& st) {
+    uint32_t ev = (pair_events(c, v.x) & 0xffu) | ((pair_events(v.x, v.y) & 0xffu) << 8) |
+                  ((pair_events(v.y, v.z) & 0xffu) << 16) | (pair_events(v.z, v.w) << 24);
+    // bit pair t <-> the byte pair (p + t - 1, p + t): it must start at >= 0 and end at <= L - 1
+    if (p <= 0 || p + 16 > L) {
+        const int lo = clamp16(1 - p), hi = clamp16(L - p);
+        const uint32_t mhi = hi >= 16 ? 0xffffffffu : (1u << (2 * hi)) - 1u;
+        const uint32_t mlo = lo >= 16 ? 0xffffffffu : (1u << (2 * lo)) - 1u;
+        ev &= mhi & ~mlo;
+    }
+    uint32_t sb = ev & 0x55555555u, cb = ev & 0xaaaaaaaau;
+    if (st.n_c == 0u) {                            // still on the first line: note its first two spaces
+        uint32_t z = mask16(eqf(v.x, K.sp, K), eqf(v.y, K.sp, K), eqf(v.z, K.sp, K), eqf(v.w, K.sp, K));
+        if (p < 0 || p + 16 > L) z &= rng16(-p, L - p);
+        if (cb) z &= below(max(((__ffs(cb) - 1) >> 1) - 1, 0));        // spaces before the line's CR only
+        if (z && st.sp1 < 0) { st.sp1 = p + __ffs(z) - 1; z &= z - 1u; }
+        if (z && st.sp1 >= 0 && st.sp2 < 0) st.sp2 = p + __ffs(z) - 1;
+    }
+    const int q = p - 1;
+    const uint32_t sb0 = sb, n_s0 = st.n_s;
+    if (sb) {                                      // the common vector holds at most one ": " ...
+        const int b = __ffs(sb) - 1;
+        sb &= sb - 1u;
+        sp[min(st.n_s, (uint32_t)kSepCap - 1u) * 32] = (uint16_t)(q + (b >> 1));
+        st.n_s++;
+    }
+    if (cb) {                                      // ... and at most one CRLF: straight-line code
+        const int b = __ffs(cb) - 1;
+        cb &= cb - 1u;
+        const int pos = q + (b >> 1);
+        if (pos == st.last_cr + 2 && st.n_c >= 2u) { st.T = st.last_cr; return; }     // empty line after the first line: CRLFCRLF
+        const uint32_t seen = n_s0 + (uint32_t)__popc(sb0 & ((1u << b) - 1u));       // ": " before this CR
+        if (st.n_c == 0u) st.s_skip = seen; else st.bad |= seen - st.s_prev - 1u;     // a header line must add exactly one
+        st.s_prev = seen;
+        cr[min(st.n_c, (uint32_t)kCrCap - 1u) * 32] = (uint16_t)pos;
+        st.n_c++; st.last_cr = pos;
+    }
+    if (sb | cb) {                                 // the rest (a terminator inside one vector, short lines)
+        while (sb) {
+            const int b = __ffs(sb) - 1;
+            sb &= sb - 1u;
+            sp[min(st.n_s, (uint32_t)kSepCap - 1u) * 32] = (uint16_t)(q + (b >> 1));
+            st.n_s++;
+        }
+        while (cb) {
+            const int b = __ffs(cb) - 1;
+            cb &= cb - 1u;
+            const int pos = q + (b >> 1);
+            if (pos == st.last_cr + 2 && st.n_c >= 2u) { st.T = st.last_cr; return; }
+            const uint32_t seen = n_s0 + (uint32_t)__popc(sb0 & ((1u << b) - 1u));
+            if (st.n_c == 0u) st.s_skip = seen; else st.bad |= seen - st.s_prev - 1u;
+            st.s_prev = seen;
+            cr[min(st.n_c, (uint32_t)kCrCap - 1u) * 32] = (uint16_t)pos;
+            st.n_c++; st.last_cr = pos;
+        }
+    }
+}
+
 __device__ __forceinline__ void scan_lists(const uint8_t* m, const int L, uint16_t* cr, uint16_t* sp, const SwarK& K, LaneScan& o) {
     const int lead = (int)(reinterpret_cast<uintptr_t>(m) & 31);
     const uint4* vp = reinterpret_cast<const uint4*>(m - lead);
-    const int nvec = 2 * ((lead + L + 31) >> 5);
-    int p = -lead;                                 // message position of byte 0 of the current vector
-    int idx = -1, T = -1, last_cr = -4, sp1 = -1, sp2 = -1;
-    uint32_t n_c = 0, n_s = 0;
-    uint32_t s_skip = 0, s_prev = 0, first_bad = 0xffffffffu, bad_cnt = 0;   // on-line "exactly one ': ' per line" check
-    uint4 v = __ldg(vp), v1 = __ldg(vp + 1);
-    for (int i = 0; i < nvec && p < L; i++, p += 16) {
-        uint4 nx = make_uint4(0u, 0u, 0u, 0u);
-        if (i + 2 < nvec) nx = __ldg(vp + i + 2);                      // one 32-byte sector ahead
-#if SHL_OPT_PF_L2
-        if ((i & 7) == 0 && i + 16 < nvec) prefetch_l2(vp + i + 16);   // and the line after next on its way to L2
-#endif
-        uint32_t ev = (pair_events(v.x, v.y) & 0xffu) | ((pair_events(v.y, v.z) & 0xffu) << 8) |
-                      ((pair_events(v.z, v.w) & 0xffu) << 16) | (pair_events(v.w, v1.x) << 24);
-        if (p < 0 || p + 17 > L) {                 // a pair may start at message positions [0, L-1)
-            const int lo = clamp16(-p), hi = clamp16(L - 1 - p);
-            const uint32_t mhi = hi >= 16 ? 0xffffffffu : (1u << (2 * hi)) - 1u;
-            const uint32_t mlo = lo >= 16 ? 0xffffffffu : (1u << (2 * lo)) - 1u;
-            ev &= mhi & ~mlo;
-        }
-        uint32_t sb = ev & 0x55555555u, cb = ev & 0xaaaaaaaau;
-        if (idx < 0) {                             // still on the first line: note its first two spaces
-            uint32_t z = mask16(eqf(v.x, K.sp, K), eqf(v.y, K.sp, K), eqf(v.z, K.sp, K), eqf(v.w, K.sp, K));
-            if (p < 0 || p + 16 > L) z &= rng16(-p, L - p);
-            if (cb) z &= below((__ffs(cb) - 1) >> 1);
-            if (z && sp1 < 0) { sp1 = p + __ffs(z) - 1; z &= z - 1u; }
-            if (z && sp1 >= 0 && sp2 < 0) sp2 = p + __ffs(z) - 1;
-        }
-        const uint32_t sb0 = sb, n_s0 = n_s;
-        while (sb) {                               // ": " positions (of the ':')
-            const int b = __ffs(sb) - 1;
-            sb &= sb - 1u;
-            sp[min(n_s, (uint32_t)kSepCap - 1u) * 32] = (uint16_t)(p + (b >> 1));
-            n_s++;
-        }
-        while (cb) {                               // CRLF positions (of the CR)
-            const int b = __ffs(cb) - 1;
-            cb &= cb - 1u;
-            const int pos = p + (b >> 1);
-            if (pos == last_cr + 2 && n_c >= 2u) { T = last_cr; break; }     // empty line after the first line: CRLFCRLF
-            const uint32_t seen = n_s0 + (uint32_t)__popc(sb0 & ((1u << b) - 1u));   // ": " before this CR
-            if (n_c == 0u) { idx = pos; s_skip = seen; }
-            else if (seen - s_prev != 1u && first_bad == 0xffffffffu) { first_bad = n_c - 1u; bad_cnt = seen - s_prev; }
-            s_prev = seen;
-            cr[min(n_c, (uint32_t)kCrCap - 1u) * 32] = (uint16_t)pos;
-            n_c++; last_cr = pos;
-        }
-        if (T >= 0) break;
-        v = v1; v1 = nx;
+    const int nsec = (lead + L + 31) >> 5;         // 32-byte sectors that hold message bytes
+    int p = -lead;                                 // message position of byte 0 of the current sector
+    ScanState st; st.T = -1; st.last_cr = -4; st.sp1 = st.sp2 = -1; st.n_c = st.n_s = st.s_prev = st.s_skip = st.bad = 0u;
+    uint32_t c = 0u;                               // word before the current vector (masked off in sector 0)
+    uint4 a0 = __ldg(vp), b0 = __ldg(vp + 1), a1, b1;
+    a1 = b1 = make_uint4(0u, 0u, 0u, 0u);
+#if SHL_OPT_STEP16
+    for (int i = 0; i < 2 * nsec && p < L; i++, p += 16) {     // one vector per trip, the next sector's in flight
+        if (i + 2 < 2 * nsec) a1 = __ldg(vp + i + 2);
+        scan_step(a0, c, p, L, cr, sp, K, st);
+        if (st.T >= 0) break;
+        c = a0.w; a0 = b0; b0 = a1;
     }
-    o.idx = idx; o.T = T; o.n_c = n_c; o.n_s = n_s; o.sp1 = sp1; o.sp2 = sp2;
-    o.s_skip = s_skip; o.first_bad = first_bad; o.bad_cnt = bad_cnt;
-    o.ovf = n_c > (uint32_t)kCrCap || n_s > (uint32_t)kSepCap;       // the lists are incomplete: scalar path
+#elif !SHL_OPT_UNROLL2
+    for (int s = 0; s < nsec; s++, p += 32, vp += 2) {
+        if (s + 1 < nsec) { a1 = __ldg(vp + 2); b1 = __ldg(vp + 3); }
+        scan_step(a0, c, p, L, cr, sp, K, st);
+        if (st.T >= 0) break;
+        scan_step(b0, a0.w, p + 16, L, cr, sp, K, st);
+        if (st.T >= 0) break;
+        c = b0.w; a0 = a1; b0 = b1;
+    }
+#else
+    // two sectors per trip, the registers swap roles instead of being copied
+    for (int s = 0; s < nsec; s += 2, p += 64, vp += 4) {
+        if (s + 1 < nsec) { a1 = __ldg(vp + 2); b1 = __ldg(vp + 3); }
+        scan_step(a0, c, p, L, cr, sp, K, st);
+        if (st.T >= 0) break;
+        scan_step(b0, a0.w, p + 16, L, cr, sp, K, st);
+        if (st.T >= 0 || s + 1 >= nsec) break;
+        c = b0.w;
+        if (s + 2 < nsec) { a0 = __ldg(vp + 4); b0 = __ldg(vp + 5); }
+        scan_step(a1, c, p + 32, L, cr, sp, K, st);
+        if (st.T >= 0) break;
+        scan_step(b1, a1.w, p + 48, L, cr, sp, K, st);
+        if (st.T >= 0) break;
+        c = b1.w;
+    }
+#endif
+    o.T = st.T; o.n_c = st.n_c; o.n_s = st.n_s; o.sp1 = st.sp1; o.sp2 = st.sp2;
+    o.idx = st.n_c ? (int)cr[0] : -1;
+    o.s_skip = st.s_skip; o.bad = st.bad != 0u;
+    o.ovf = st.n_c > (uint32_t)kCrCap || st.n_s > (uint32_t)kSepCap;       // the lists are incomplete: scalar path
+}
+
+// "Exactly one ': ' per header line" (HttpParser.py:326-328), from the two position lists: line k
+// runs from cr[k] + 2 to cr[k + 1]; the separators are listed in position order, so line k must
+// hold the next unused one and the one after that must lie beyond the line.  Returns the number
+// of lines that become records (those before the first offender), the error code of the offender
+// (or 0) in *err, and in *s_skip how many listed separators sit inside the first line.
+__device__ __forceinline__ uint32_t count_lines(const uint16_t* cr, const uint16_t* sp, const LaneScan& sc, uint32_t* err, uint32_t* s_skip) {
+    const uint32_t n_lines = sc.n_c - 1u;
+    uint32_t j = 0;
+    while (j < sc.n_s && (int)sp[j * 32] < sc.idx) j++;
+    *s_skip = j;
+    *err = 0u;
+    uint32_t cur = j < sc.n_s ? (uint32_t)sp[j * 32] : 0xffffffffu;
+    for (uint32_t k = 0; k < n_lines; k++) {
+        const uint32_t end = cr[(k + 1u) * 32];
+        const uint32_t nxt = j + 1u < sc.n_s ? (uint32_t)sp[(j + 1u) * 32] : 0xffffffffu;
+        if (cur > end) { *err = SHL_E_HDR_NO_SEP; return k; }          // (cur == end cannot be: that byte is the CR)
+        if (nxt < end) { *err = SHL_E_HDR_MULTI_SEP; return k; }
+        cur = nxt; j++;
+    }
+    return n_lines;
 }
 
 // ----------------------------------------------------------------------------------- epilogue helpers
@@ -344,7 +427,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
         const bool force = a.force_scalar != 0;
 
         // ---- scan (lanes diverge on their own events; nothing heavy happens in here)
-        LaneScan sc; sc.idx = sc.T = sc.sp1 = sc.sp2 = -1; sc.n_c = sc.n_s = sc.s_skip = sc.bad_cnt = 0; sc.first_bad = 0xffffffffu; sc.ovf = false;
+        LaneScan sc; sc.idx = sc.T = sc.sp1 = sc.sp2 = -1; sc.n_c = sc.n_s = sc.s_skip = 0u; sc.ovf = sc.bad = false;
         if (L > 0) scan_lists(m, L, cr, sp, K, sc);
 
 #ifdef SHL_EXP_SCANONLY
@@ -357,7 +440,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
         r.first_line_len = r.headers_len = r.sp1 = r.sp2 = r.fl_end = r.slash = r.n_headers = 0;
         r.status_code = 0; r.content_len = 0;
         WellKnown wk; wk.n_te = wk.n_cl = 0; wk.te_vs = wk.te_ve = wk.cl_vs = wk.cl_ve = 0;
-        uint32_t n_hdr = 0, hdr_err = 0;
+        uint32_t n_hdr = 0, hdr_err = 0, s_skip = 0;
         int h0 = 0, T = -1;
         bool get_or_head = false, slow = false, hdr_state = false;   // hdr_state: the header block will be tokenised
         if (L == 0) r.status |= SHL_S_EMPTY;
@@ -393,12 +476,12 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
                             hdr_err = headers_scalar(m, h0, T + 4, nullptr, 1, 0u, &n2, &w2);
                             wk = w2; n_hdr = n2;
                         } else {
-                            // the scan already checked "exactly one ': ' per line" as it went: lines
-                            // before the first offender are the records; line k's separator is the
-                            // (s_skip + k)-th listed one (s_skip = those inside the first line)
-                            const uint32_t n_lines = sc.n_c - 1u;
-                            n_hdr = min(n_lines, sc.first_bad);
-                            if (sc.first_bad < n_lines) hdr_err = sc.bad_cnt ? (uint32_t)SHL_E_HDR_MULTI_SEP : (uint32_t)SHL_E_HDR_NO_SEP;
+                            // lines before the first one that does not hold exactly one ": " are the
+                            // records; line k's separator is the (s_skip + k)-th listed one
+                            // (the scan kept a flag while it listed them; only a block that
+                            // tripped it is walked again to find the offender)
+                            if (sc.bad) n_hdr = count_lines(cr, sp, sc, &hdr_err, &s_skip);
+                            else { n_hdr = sc.n_c - 1u; s_skip = sc.s_skip; }
                         }
                     }
                 }
@@ -439,7 +522,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
                     for (int j = 0; j < kB; j++) {
                         sepv[j] = endv[j] = 0; c0v[j] = c1v[j] = 'x';
                         if (k0 + j < nh) {
-                            sepv[j] = sp[(sc.s_skip + k0 + j) * 32]; endv[j] = cr[(k0 + j + 1) * 32];
+                            sepv[j] = sp[(s_skip + k0 + j) * 32]; endv[j] = cr[(k0 + j + 1) * 32];
 #ifndef SHL_EXP_NOPEEK
                             if (sepv[j] + 2 < endv[j]) { c0v[j] = ldb(m + sepv[j] + 2); c1v[j] = ldb(m + endv[j] - 1); }
 #endif
@@ -457,8 +540,9 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
                             const int klen = sep - ls;
                             const uint32_t lo = (uint32_t)ls | ((uint32_t)klen << 16), hi = (uint32_t)vs | ((uint32_t)(ve - vs) << 16);
                             *reinterpret_cast<uint2*>(out + k0 + j) = make_uint2(lo, hi);
-                            if (klen == 14) { if (span_eq_lower(m, ls, sep, "content-length")) { if (!wk.n_cl) { wk.cl_vs = vs; wk.cl_ve = ve; } wk.n_cl++; } }
-                            else if (klen == 17) { if (span_eq_lower(m, ls, sep, "transfer-encoding")) { if (!wk.n_te) { wk.te_vs = vs; wk.te_ve = ve; } wk.n_te++; } }
+                            const uint32_t k0c = (klen == 14 || klen == 17) ? (ldb(m + ls) | 32u) : 0u;   // first letter screens the literal compare
+                            if (klen == 14 && k0c == 'c') { if (span_eq_lower(m, ls, sep, "content-length")) { if (!wk.n_cl) { wk.cl_vs = vs; wk.cl_ve = ve; } wk.n_cl++; } }
+                            else if (klen == 17 && k0c == 't') { if (span_eq_lower(m, ls, sep, "transfer-encoding")) { if (!wk.n_te) { wk.te_vs = vs; wk.te_ve = ve; } wk.n_te++; } }
                             ls = end + 2;
                         }
                     }

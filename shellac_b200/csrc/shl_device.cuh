@@ -25,21 +25,53 @@ __device__ __forceinline__ int hexval(uint32_t c) {
 
 __device__ __forceinline__ uint32_t ldb(const uint8_t* p) { return (uint32_t)__ldg(p); }
 
+// unaligned little-endian 32-bit load (may touch up to 3 bytes past p+4, inside the arena padding)
+__device__ __forceinline__ uint32_t ld32u(const uint8_t* p) {
+    const uint32_t* a = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(p) & ~(uintptr_t)3);
+    const int sh = (int)(reinterpret_cast<uintptr_t>(p) & 3) * 8;
+    const uint32_t lo = __ldg(a);
+    const uint32_t hi = sh ? __ldg(a + 1) : 0u;
+    return __funnelshift_r(lo, hi, sh);
+}
+
+// ASCII lower() of four packed bytes (bytes >= 0x80 are left alone, like Python 2's str.lower in the C locale)
+__device__ __forceinline__ uint32_t lower4(uint32_t x) {
+    const uint32_t t = x & 0x7f7f7f7fu;
+    const uint32_t ge_A = t + 0x3f3f3f3fu;                 // bit 7 of a byte set iff t >= 'A'
+    const uint32_t gt_Z = t + 0x25252525u;                 // ... iff t > 'Z'
+    return x | ((ge_A & ~gt_Z & ~x & 0x80808080u) >> 2);
+}
+
+// p[0:n] == lit (ci: lower(p[0:n]) == lit, lit lower-case).  ONE out-of-line copy, word at a time:
+// the literal compares used to be unrolled byte loops inlined at every call site, a quarter of
+// the route kernel's code, which the instruction cache paid for (profiles/r01/v8_notes).
+__device__ __noinline__ bool span_eq_words(const uint8_t* p, const char* lit, int n, bool ci) {
+    int k = 0;
+    for (; k + 4 <= n; k += 4) {
+        uint32_t x = ld32u(p + k);
+        const uint32_t y = (uint32_t)(uint8_t)lit[k] | ((uint32_t)(uint8_t)lit[k + 1] << 8) |
+                           ((uint32_t)(uint8_t)lit[k + 2] << 16) | ((uint32_t)(uint8_t)lit[k + 3] << 24);
+        if (ci) x = lower4(x);
+        if (x != y) return false;
+    }
+    for (; k < n; k++) {
+        uint32_t c = ldb(p + k);
+        if (ci) c = lower(c);
+        if (c != (uint32_t)(uint8_t)lit[k]) return false;
+    }
+    return true;
+}
 // m[a:b] == lit  (exact)
 template <int N>
 __device__ __forceinline__ bool span_eq(const uint8_t* m, int64_t a, int64_t b, const char (&lit)[N]) {
     if (b - a != N - 1) return false;
-#pragma unroll
-    for (int k = 0; k < N - 1; k++) if (ldb(m + a + k) != (uint32_t)(uint8_t)lit[k]) return false;
-    return true;
+    return span_eq_words(m + a, lit, N - 1, false);
 }
 // lower(m[a:b]) == lit  (lit is lower-case)
 template <int N>
 __device__ __forceinline__ bool span_eq_lower(const uint8_t* m, int64_t a, int64_t b, const char (&lit)[N]) {
     if (b - a != N - 1) return false;
-#pragma unroll
-    for (int k = 0; k < N - 1; k++) if (lower(ldb(m + a + k)) != (uint32_t)(uint8_t)lit[k]) return false;
-    return true;
+    return span_eq_words(m + a, lit, N - 1, true);
 }
 
 // float(s) accepts?  [ws] [+-] (digits [. digits*] | . digits) [(e|E) [+-] digits] [ws]  |  inf / infinity / nan
@@ -151,22 +183,21 @@ __device__ __forceinline__ void md5_key(const uint8_t* key, uint32_t n, uint32_t
     const uint32_t o = (uint32_t)(reinterpret_cast<uintptr_t>(key) & 3);
     const int sh = (int)o * 8;
     const uint32_t nblk = (n + 8u) / 64u + 1u;
-    // aligned word j holds key bytes [4j-o, 4j-o+4); only touch words that hold a key byte
+    // aligned word j holds key bytes [4j-o, 4j-o+4); only words that hold a key byte are touched.
+    // Straight-line per word (lanes hold keys of different lengths): key word gi is data below
+    // wn, the word with the 0x80 pad at wn, zero above.
+    const uint32_t nw = (n + o + 3u) >> 2, wn = n >> 2;
+    const uint32_t r8 = (n & 3u) * 8u, km = (1u << r8) - 1u, pd = 0x80u << r8;
     uint32_t lo = (n > 0u) ? __ldg(ap) : 0u;
     for (uint32_t blk = 0; blk < nblk; blk++) {
         uint32_t w[16];
 #pragma unroll
         for (int i = 0; i < 16; i++) {
             const uint32_t gi = blk * 16u + (uint32_t)i;        // key word index
-            const uint32_t pos = gi * 4u;                        // key byte offset of this word
-            uint32_t x = 0;
-            if (pos < n) {
-                const uint32_t hi = (4u * (gi + 1u) < n + o) ? __ldg(ap + gi + 1u) : 0u;
-                x = o ? __funnelshift_r(lo, hi, sh) : lo;
-                lo = hi;
-                const uint32_t rem = n - pos;                    // valid bytes in x (>= 1)
-                if (rem < 4u) x = (x & ((1u << (8u * rem)) - 1u)) | (0x80u << (8u * rem));
-            } else if (pos == n) x = 0x80u;
+            const uint32_t hi = (gi + 1u < nw) ? __ldg(ap + gi + 1u) : 0u;
+            uint32_t x = __funnelshift_r(lo, hi, sh);
+            lo = hi;
+            x = gi < wn ? x : (gi == wn ? ((x & km) | pd) : 0u);
             if (blk == nblk - 1u) { if (i == 14) x = n << 3; if (i == 15) x = n >> 29; }
             w[i] = x;
         }

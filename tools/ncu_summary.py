@@ -22,10 +22,10 @@ for r in rows[2:3]:
             if h == w:
                 print('%-72s %s %s' % (w, r[i], units[i]))
     stall = [(float(r[i].replace(',', '')), h) for i, h in enumerate(hdr)
-             if 'issue_stalled' in h and h.endswith('_per_warp_active.pct') and r[i]]
-    print('top stalls (pct of warp-active):')
+             if 'average_warps_issue_stalled' in h and h.endswith('_per_issue_active.ratio') and r[i]]
+    print('top stalls (warps stalled per issue-active cycle):')
     for v, h in sorted(stall, reverse=True)[:8]:
-        print('   %6.1f  %s' % (v, h.replace('smsp__warp_issue_stalled_', '').replace('_per_warp_active.pct', '')))
+        print('   %6.2f  %s' % (v, h.replace('smsp__average_warps_issue_stalled_', '').replace('_per_issue_active.ratio', '')))
 sass = subprocess.run(['ncu', '-i', rep, '--page', 'source', '--csv', '--print-source', 'sass'], capture_output=True, text=True).stdout
 rows = list(csv.reader(sass.splitlines()))
 hi = [i for i, r in enumerate(rows) if r and r[0] == 'Address']
