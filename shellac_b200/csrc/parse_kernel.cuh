@@ -29,26 +29,11 @@
 
 namespace shl {
 
-#ifndef SHL_OPT_PF_L2
-#define SHL_OPT_PF_L2 0
-#endif
-#ifndef SHL_OPT_PF_URL
-#define SHL_OPT_PF_URL 0
-#endif
 #ifndef SHL_OPT_RINGDIR
 #define SHL_OPT_RINGDIR 1
 #endif
 #ifndef SHL_OPT_MINBLOCKS
 #define SHL_OPT_MINBLOCKS 8
-#endif
-#ifndef SHL_OPT_EVFIRST
-#define SHL_OPT_EVFIRST 1
-#endif
-#ifndef SHL_OPT_UNROLL2
-#define SHL_OPT_UNROLL2 0
-#endif
-#ifndef SHL_OPT_STEP16
-#define SHL_OPT_STEP16 0
 #endif
 #ifndef SHL_OPT_BATCH
 #define SHL_OPT_BATCH 2
@@ -231,8 +216,11 @@ __device__ __forceinline__ uint32_t pair_events(uint32_t pv, uint32_t w) {
     return __umulhi((fc & 0x80808080u) | (fs & 0x40404040u), 0x04104100u);   // [s0 c0 s1 c1 s2 c2 s3 c3] + stray bits above bit 7
 }
 
-__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
-__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
+// ... of one 16-byte vector (c = the word before it): bit pair t <-> the byte pair that starts at byte t - 1
+__device__ __forceinline__ uint32_t vec_events(const uint32_t c, const uint4& v) {
+    return (pair_events(c, v.x) & 0xffu) | ((pair_events(v.x, v.y) & 0xffu) << 8) |
+           ((pair_events(v.y, v.z) & 0xffu) << 16) | (pair_events(v.z, v.w) << 24);
+}
 
 // Running state of one lane's scan.  Events are only LISTED here (positions of the CR of every
 // CRLF, of the ':' of every ": "); which separator belongs to which line is worked out afterwards
@@ -246,8 +234,7 @@ struct ScanState {
 // One 16-byte vector v at message position p (byte 0 of v), c = the word before it.
 __device__ __forceinline__ void scan_step(const uint4& v, const uint32_t c, const int p, const int L,
                                           uint16_t* cr, uint16_t* sp, const SwarK& K, ScanState& st) {
-    uint32_t ev = (pair_events(c, v.x) & 0xffu) | ((pair_events(v.x, v.y) & 0xffu) << 8) |
-                  ((pair_events(v.y, v.z) & 0xffu) << 16) | (pair_events(v.z, v.w) << 24);
+    uint32_t ev = vec_events(c, v);
     // bit pair t <-> the byte pair (p + t - 1, p + t): it must start at >= 0 and end at <= L - 1
     if (p <= 0 || p + 16 > L) {
         const int lo = clamp16(1 - p), hi = clamp16(L - p);
@@ -312,14 +299,6 @@ __device__ __forceinline__ void scan_lists(const uint8_t* m, const int L, uint16
     uint32_t c = 0u;                               // word before the current vector (masked off in sector 0)
     uint4 a0 = __ldg(vp), b0 = __ldg(vp + 1), a1, b1;
     a1 = b1 = make_uint4(0u, 0u, 0u, 0u);
-#if SHL_OPT_STEP16
-    for (int i = 0; i < 2 * nsec && p < L; i++, p += 16) {     // one vector per trip, the next sector's in flight
-        if (i + 2 < 2 * nsec) a1 = __ldg(vp + i + 2);
-        scan_step(a0, c, p, L, cr, sp, K, st);
-        if (st.T >= 0) break;
-        c = a0.w; a0 = b0; b0 = a1;
-    }
-#elif !SHL_OPT_UNROLL2
     for (int s = 0; s < nsec; s++, p += 32, vp += 2) {
         if (s + 1 < nsec) { a1 = __ldg(vp + 2); b1 = __ldg(vp + 3); }
         scan_step(a0, c, p, L, cr, sp, K, st);
@@ -328,23 +307,6 @@ __device__ __forceinline__ void scan_lists(const uint8_t* m, const int L, uint16
         if (st.T >= 0) break;
         c = b0.w; a0 = a1; b0 = b1;
     }
-#else
-    // two sectors per trip, the registers swap roles instead of being copied
-    for (int s = 0; s < nsec; s += 2, p += 64, vp += 4) {
-        if (s + 1 < nsec) { a1 = __ldg(vp + 2); b1 = __ldg(vp + 3); }
-        scan_step(a0, c, p, L, cr, sp, K, st);
-        if (st.T >= 0) break;
-        scan_step(b0, a0.w, p + 16, L, cr, sp, K, st);
-        if (st.T >= 0 || s + 1 >= nsec) break;
-        c = b0.w;
-        if (s + 2 < nsec) { a0 = __ldg(vp + 4); b0 = __ldg(vp + 5); }
-        scan_step(a1, c, p + 32, L, cr, sp, K, st);
-        if (st.T >= 0) break;
-        scan_step(b1, a1.w, p + 48, L, cr, sp, K, st);
-        if (st.T >= 0) break;
-        c = b1.w;
-    }
-#endif
     o.T = st.T; o.n_c = st.n_c; o.n_s = st.n_s; o.sp1 = st.sp1; o.sp2 = st.sp2;
     o.idx = st.n_c ? (int)cr[0] : -1;
     o.s_skip = st.s_skip; o.bad = st.bad != 0u;
@@ -371,6 +333,129 @@ __device__ __forceinline__ uint32_t count_lines(const uint16_t* cr, const uint16
         cur = nxt; j++;
     }
     return n_lines;
+}
+
+// ----------------------------------------------------------------------------------- scan: one GROUP, one warp
+// The 32 messages of a group usually lie back to back in the arena (that is how every packer in
+// this repo, and a recv() loop, lays them out).  Then the warp does not scan 32 messages in 32
+// lanes, it scans ONE span of bytes with 32 lanes:
+//   phase A  lane l classifies bytes [1024 r + 32 l, +32) of the span in row r (fully coalesced
+//            loads, every lane busy until the last row, no per-message edges), and the set bits
+//            are compacted, in position order, into two flat u16 lists for the whole group
+//            (positions relative to the span) with one warp prefix sum per row;
+//   phase B  lane j finds message j's slice of the lists by binary search and walks its CRLFs
+//            (first line end, CRLFCRLF, one ": " per line) with all lanes doing the same thing.
+// A group that does not qualify (unordered or overlapping messages, a span over kSpanMax, more
+// events than the lists hold) is scanned message-per-lane by scan_lists, with identical results.
+constexpr uint32_t kSpanMax = 32768u;
+constexpr uint32_t kCrFlat = kCrCap * 32, kSepFlat = kSepCap * 32;
+
+// lists the events of span[0:nbytes) (A0 is 32-byte aligned); false = the lists overflowed
+__device__ __forceinline__ bool group_list_events(const uint8_t* A0, const uint32_t nbytes, uint16_t* crl, uint16_t* sepl,
+                                                  const int lane, uint32_t& n_c_tot, uint32_t& n_s_tot) {
+    uint32_t base_c = 0u, base_s = 0u, prev_last = 0u;
+    uint32_t boff = (uint32_t)lane * 32u;
+    uint4 va = make_uint4(0u, 0u, 0u, 0u), vb = va;
+    if (boff < nbytes) { va = __ldg(reinterpret_cast<const uint4*>(A0 + boff)); vb = __ldg(reinterpret_cast<const uint4*>(A0 + boff + 16)); }
+    bool fits = true;
+    for (; boff - (uint32_t)lane * 32u < nbytes; boff += 1024u) {          // warp-uniform trip count
+        uint4 na = make_uint4(0u, 0u, 0u, 0u), nb = na;
+        if (boff + 1024u < nbytes) {                                        // next row in flight
+            na = __ldg(reinterpret_cast<const uint4*>(A0 + boff + 1024u)); nb = __ldg(reinterpret_cast<const uint4*>(A0 + boff + 1040u));
+        }
+        uint32_t c = __shfl_up_sync(SHL_FULL, vb.w, 1);
+        if (lane == 0) c = prev_last;
+        prev_last = __shfl_sync(SHL_FULL, vb.w, 31);
+        const uint32_t ev0 = vec_events(c, va), ev1 = vec_events(va.w, vb);
+        uint32_t cb0 = ev0 & 0xaaaaaaaau, sb0 = ev0 & 0x55555555u, cb1 = ev1 & 0xaaaaaaaau, sb1 = ev1 & 0x55555555u;
+        const uint32_t cnt = (uint32_t)(__popc(cb0) + __popc(cb1)) | ((uint32_t)(__popc(sb0) + __popc(sb1)) << 16);
+        uint32_t inc = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(SHL_FULL, inc, d); if (lane >= d) inc += t; }
+        const uint32_t tot = __shfl_sync(SHL_FULL, inc, 31);
+        if (base_c + (tot & 0xffffu) > kCrFlat || base_s + (tot >> 16) > kSepFlat) { fits = false; break; }
+        uint32_t ic = base_c + ((inc - cnt) & 0xffffu), is = base_s + ((inc - cnt) >> 16);
+        const uint32_t q0 = boff - 1u, q1 = boff + 15u;
+        // a 16-byte vector rarely holds more than one event of a kind: the first of each is written by
+        // straight-line predicated code, the loops only run for what is left (CRLFCRLF, short lines)
+        if (cb0) { const int b = __ffs(cb0) - 1; cb0 &= cb0 - 1u; crl[ic++] = (uint16_t)(q0 + (uint32_t)(b >> 1)); }
+        if (sb0) { const int b = __ffs(sb0) - 1; sb0 &= sb0 - 1u; sepl[is++] = (uint16_t)(q0 + (uint32_t)(b >> 1)); }
+        if (cb0 | sb0) {
+            while (cb0) { const int b = __ffs(cb0) - 1; cb0 &= cb0 - 1u; crl[ic++] = (uint16_t)(q0 + (uint32_t)(b >> 1)); }
+            while (sb0) { const int b = __ffs(sb0) - 1; sb0 &= sb0 - 1u; sepl[is++] = (uint16_t)(q0 + (uint32_t)(b >> 1)); }
+        }
+        if (cb1) { const int b = __ffs(cb1) - 1; cb1 &= cb1 - 1u; crl[ic++] = (uint16_t)(q1 + (uint32_t)(b >> 1)); }
+        if (sb1) { const int b = __ffs(sb1) - 1; sb1 &= sb1 - 1u; sepl[is++] = (uint16_t)(q1 + (uint32_t)(b >> 1)); }
+        if (cb1 | sb1) {
+            while (cb1) { const int b = __ffs(cb1) - 1; cb1 &= cb1 - 1u; crl[ic++] = (uint16_t)(q1 + (uint32_t)(b >> 1)); }
+            while (sb1) { const int b = __ffs(sb1) - 1; sb1 &= sb1 - 1u; sepl[is++] = (uint16_t)(q1 + (uint32_t)(b >> 1)); }
+        }
+        base_c += tot & 0xffffu; base_s += tot >> 16;
+        va = na; vb = nb;
+    }
+    n_c_tot = base_c; n_s_tot = base_s;
+    return fits;
+}
+
+// first index i in list[0:n) with list[i] >= key
+__device__ __forceinline__ uint32_t list_lower_bound(const uint16_t* list, const uint32_t n, const uint32_t key) {
+    uint32_t lo = 0u, hi = n;
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if ((uint32_t)list[mid] < key) lo = mid + 1u; else hi = mid;
+    }
+    return lo;
+}
+
+// What phase B hands to the epilogue for one message.
+struct GroupWalk {
+    int idx, T;                        // message-relative positions of the first line's CR / the CR that ends the header block
+    uint32_t n_c;                      // CRLFs up to and including T's (header lines + 1)
+    uint32_t ic0, js0;                 // list index of the first line's CR / of the first header line's ": "
+    uint32_t first_bad, err;           // first header line without exactly one ": " (or 0xffffffff) and its error code
+};
+
+// message [s0, s0 + L) of the span: HttpParser.parse's framing decisions from the two lists
+__device__ __forceinline__ void group_walk(const uint16_t* crl, const uint16_t* sepl, const uint32_t n_c_tot, const uint32_t n_s_tot,
+                                           const uint32_t s0, const int L, GroupWalk& o) {
+    o.idx = o.T = -1; o.n_c = 0u; o.first_bad = 0xffffffffu; o.err = 0u;
+    const uint32_t lim = s0 + (uint32_t)max(L, 2) - 2u;                // last position a pair of this message may start at
+    uint32_t k = list_lower_bound(crl, n_c_tot, s0);
+    uint32_t js = list_lower_bound(sepl, n_s_tot, s0);
+    o.ic0 = k; o.js0 = js;
+    if (L < 2 || k >= n_c_tot) return;
+    uint32_t prev = crl[k];
+    if (prev > lim) return;
+    o.idx = (int)(prev - s0); o.n_c = 1u;
+    while (js < n_s_tot && (uint32_t)sepl[js] < prev) js++;            // ": " inside the first line are not separators
+    o.js0 = js;
+    uint32_t cur = js < n_s_tot ? (uint32_t)sepl[js] : 0xffffffffu;
+    for (k++; k < n_c_tot; k++) {
+        const uint32_t pos = crl[k];
+        if (pos > lim) break;
+        if (pos == prev + 2u && o.n_c >= 2u) { o.T = (int)(prev - s0); break; }       // empty line after the first line: CRLFCRLF
+        if (o.first_bad == 0xffffffffu) {                               // the line [prev + 2, pos) must hold exactly one ": "
+            const uint32_t nxt = js + 1u < n_s_tot ? (uint32_t)sepl[js + 1u] : 0xffffffffu;
+            if (cur > pos) { o.first_bad = o.n_c - 1u; o.err = SHL_E_HDR_NO_SEP; }
+            else if (nxt < pos) { o.first_bad = o.n_c - 1u; o.err = SHL_E_HDR_MULTI_SEP; }
+            else { cur = nxt; js++; }
+        }
+        prev = pos; o.n_c++;
+    }
+}
+
+// the first two spaces of m[0:idx) (the scan of the per-lane path notes them as it goes)
+__device__ __forceinline__ void first_two_spaces(const uint8_t* m, const int idx, const SwarK& K, int& sp1, int& sp2) {
+    const int lead = (int)(reinterpret_cast<uintptr_t>(m) & 15);
+    const uint4* vp = reinterpret_cast<const uint4*>(m - lead);
+    sp1 = sp2 = -1;
+    for (int p = -lead; p < idx && sp2 < 0; p += 16, vp++) {
+        const uint4 v = __ldg(vp);
+        uint32_t z = mask16(eqf(v.x, K.sp, K), eqf(v.y, K.sp, K), eqf(v.z, K.sp, K), eqf(v.w, K.sp, K));
+        if (p < 0 || p + 16 > idx) z &= rng16(-p, idx - p);
+        if (z && sp1 < 0) { sp1 = p + __ffs(z) - 1; z &= z - 1u; }
+        if (z && sp1 >= 0 && sp2 < 0) sp2 = p + __ffs(z) - 1;
+    }
 }
 
 // ----------------------------------------------------------------------------------- epilogue helpers
@@ -426,14 +511,36 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
         uint16_t* sp = &s_sp[warp][lane];
         const bool force = a.force_scalar != 0;
 
-        // ---- scan (lanes diverge on their own events; nothing heavy happens in here)
+        // ---- scan: the whole group as one span of bytes when its messages lie in order ...
         LaneScan sc; sc.idx = sc.T = sc.sp1 = sc.sp2 = -1; sc.n_c = sc.n_s = sc.s_skip = 0u; sc.ovf = sc.bad = false;
-        if (L > 0) scan_lists(m, L, cr, sp, K, sc);
+        GroupWalk gw; gw.idx = gw.T = -1; gw.n_c = gw.ic0 = gw.js0 = gw.err = 0u; gw.first_bad = 0xffffffffu;
+        uint32_t s0 = 0u;                                      // my message's position in the span
+        bool coal = false;
+        if (!force && __shfl_sync(SHL_FULL, (int)have, 0)) {
+            const uint8_t* p0 = a.arena + __shfl_sync(SHL_FULL, my_off, 0);
+            const uint8_t* A0 = p0 - (reinterpret_cast<uintptr_t>(p0) & 31);
+            const uint8_t* my_end = m + L;
+            const uint8_t* prev_end = reinterpret_cast<const uint8_t*>(__shfl_up_sync(SHL_FULL, reinterpret_cast<unsigned long long>(my_end), 1));
+            const bool ok = !have || ((lane == 0 || m >= prev_end) && (uint64_t)(my_end - A0) <= (uint64_t)kSpanMax);
+            if (__all_sync(SHL_FULL, ok)) {
+                const uint32_t nbytes = __reduce_max_sync(SHL_FULL, have ? (uint32_t)(my_end - A0) : 0u);
+                uint32_t nct = 0u, nst = 0u;
+                coal = group_list_events(A0, nbytes, s_cr[warp], s_sp[warp], lane, nct, nst);
+                __syncwarp();
+                if (coal) {
+                    s0 = (uint32_t)(m - A0);
+                    if (have) group_walk(s_cr[warp], s_sp[warp], nct, nst, s0, L, gw);
+                    sc.idx = gw.idx; sc.T = gw.T; sc.n_c = gw.n_c;
+                    if (gw.idx >= 0) first_two_spaces(m, gw.idx, K, sc.sp1, sc.sp2);
+                }
+            }
+        }
+        // ... else message per lane (lanes diverge on their own events; nothing heavy happens in here)
+        if (!coal && L > 0) scan_lists(m, L, cr, sp, K, sc);
+        const uint16_t* crp = coal ? &s_cr[warp][gw.ic0] : cr;     // line k ends at crp[(k + 1) * lstride] - lsub
+        const int lstride = coal ? 1 : 32;
+        const int lsub = coal ? (int)s0 : 0;
 
-#ifdef SHL_EXP_SCANONLY
-        if (have) { a.out.status[mine] = sc.n_c + sc.n_s + (uint32_t)sc.T + (uint32_t)sc.idx; }
-        if (SHL_EXP_SCANONLY) goto scan_done;
-#endif
         // ---- first line, header block bounds, line count
         Msg r;
         r.status = (3u << SHL_F_VERSION_SHIFT) | SHL_F_IS_REQUEST;
@@ -458,11 +565,6 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
                 }
                 if (fl_code) r.status |= fl_code;
                 else {
-                    if (SHL_OPT_PF_URL && kPlace && (r.status & SHL_F_IS_REQUEST)) {     // the URL is hashed at the very end: start fetching it now
-                        prefetch_l1(m + r.sp1 + 1);
-                        if (r.sp2 - r.sp1 > 32u) prefetch_l1(m + r.sp1 + 33);
-                        if (r.sp2 - r.sp1 > 64u) prefetch_l1(m + r.sp1 + 65);
-                    }
                     h0 = idx + 2;
                     T = sc.ovf ? find_term_scalar(m, h0, L) : sc.T;
                     if (T < 0) r.status |= SHL_S_INCOMPLETE_HEADERS;
@@ -480,7 +582,11 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
                             // records; line k's separator is the (s_skip + k)-th listed one
                             // (the scan kept a flag while it listed them; only a block that
                             // tripped it is walked again to find the offender)
-                            if (sc.bad) n_hdr = count_lines(cr, sp, sc, &hdr_err, &s_skip);
+                            if (coal) {
+                                const uint32_t n_lines = gw.n_c - 1u;
+                                n_hdr = min(n_lines, gw.first_bad);
+                                if (gw.first_bad < n_lines) hdr_err = gw.err;
+                            } else if (sc.bad) n_hdr = count_lines(cr, sp, sc, &hdr_err, &s_skip);
                             else { n_hdr = sc.n_c - 1u; s_skip = sc.s_skip; }
                         }
                     }
@@ -514,6 +620,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
             } else {
                 // four lines per round: all eight byte peeks are in flight before the first is needed
                 int ls = h0;
+                const uint16_t* spp = coal ? &s_sp[warp][gw.js0] : sp + s_skip * 32;   // line k's ": " is at spp[k * lstride] - lsub
                 constexpr int kB = SHL_OPT_BATCH;
                 for (uint32_t k0 = 0; k0 < nh; k0 += kB) {
                     int sepv[kB], endv[kB];
@@ -522,10 +629,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
                     for (int j = 0; j < kB; j++) {
                         sepv[j] = endv[j] = 0; c0v[j] = c1v[j] = 'x';
                         if (k0 + j < nh) {
-                            sepv[j] = sp[(s_skip + k0 + j) * 32]; endv[j] = cr[(k0 + j + 1) * 32];
-#ifndef SHL_EXP_NOPEEK
+                            sepv[j] = (int)spp[(k0 + j) * lstride] - lsub; endv[j] = (int)crp[(k0 + j + 1) * lstride] - lsub;
                             if (sepv[j] + 2 < endv[j]) { c0v[j] = ldb(m + sepv[j] + 2); c1v[j] = ldb(m + endv[j] - 1); }
-#endif
                         }
                     }
 #pragma unroll
@@ -585,9 +690,6 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
             if (a.place.node) a.place.node[mine] = node;
         }
     }
-#ifdef SHL_EXP_SCANONLY
-scan_done:
-#endif
     __syncthreads();
     if (a.code_hist && threadIdx.x < 64 && s_codes[threadIdx.x])
         atomicAdd(reinterpret_cast<unsigned long long*>(a.code_hist) + threadIdx.x, (unsigned long long)s_codes[threadIdx.x]);

@@ -133,6 +133,32 @@ def test_golden_vs_oracle_soa_all_alignments(eng, golden):
         assert_frame_equal(ar, eng.frame(ar, g, reuse_arena=True), O.orc_frame(ar, o), 'golden frame %d' % rep)
 
 
+def test_unordered_arena_takes_the_per_lane_scan(eng, golden):
+    """k_route scans a group of 32 messages as one span of bytes when they lie in index order;
+    an arena indexed back to front (or with overlapping views of the same bytes) must take the
+    message-per-lane scan instead and give the same answers."""
+    rng = np.random.default_rng(5)
+    msgs = [w['msg'] for w in golden['whole']]
+    ar = scatter_pack(eng, msgs, rng)
+    rev = Arena(ar.data, ar.off[::-1].copy(), ar.len[::-1].copy())
+    g, o = eng.parse(rev), O.orc_parse(rev)
+    assert_parse_equal(rev, g, o, 'reversed index')
+    assert_frame_equal(rev, eng.frame(rev, g, reuse_arena=True), O.orc_frame(rev, o), 'reversed index frame')
+    # every message listed twice in a row: views overlap, the group is not a span
+    dup = Arena(ar.data, np.repeat(ar.off, 2), np.repeat(ar.len, 2))
+    assert_parse_equal(dup, eng.parse(dup), O.orc_parse(dup), 'duplicated views')
+    # one group in order, the next one not: both scans inside one launch
+    mix_off, mix_len = ar.off.copy(), ar.len.copy()
+    for g0 in range(32, ar.n - 31, 64):
+        mix_off[g0:g0 + 32] = mix_off[g0:g0 + 32][::-1].copy()
+        mix_len[g0:g0 + 32] = mix_len[g0:g0 + 32][::-1].copy()
+    mix = Arena(ar.data, mix_off, mix_len)
+    eng.ring_build(['10.0.0.%d' % (i + 1) for i in range(16)])
+    pg, qg = eng.route(mix)
+    po = O.orc_parse(mix)
+    assert_parse_equal(mix, pg, po, 'alternating groups')
+
+
 def test_fresh_engines_give_the_same_records_every_time(golden):
     """Regression guard for allocation races: a fresh ctx per iteration (so stale device memory
     would show), records and record ranges checked against the oracle each time."""
