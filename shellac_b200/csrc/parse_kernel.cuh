@@ -216,10 +216,36 @@ __device__ __forceinline__ uint32_t pair_events(uint32_t pv, uint32_t w) {
     return __umulhi((fc & 0x80808080u) | (fs & 0x40404040u), 0x04104100u);   // [s0 c0 s1 c1 s2 c2 s3 c3] + stray bits above bit 7
 }
 
+#ifndef SHL_OPT_HGATHER
+#define SHL_OPT_HGATHER 1
+#endif
+// The same four pairs, gathered on the half-precision FMA pipe instead of with PRMT / LOP3 (the
+// kernel is bound by the integer ALU pipe): HSET2.BF gives 1.0 per matching half, four HFMA2 add
+// them up with power-of-two weights on top of 1024.0, whose fp16 mantissa then IS the bit field:
+// low half = [s-1 c-1 s0 c0], high half = the pairs at bytes 1 and 2, weighted 16x.
+// Returns 0x64hh64ll-style halves; (x * 0x10001) has lo + hi in byte 2.
+__device__ __forceinline__ uint32_t pair_events_h(uint32_t pv, uint32_t w) {
+    const uint32_t sh = __funnelshift_r(pv, w, 24);
+    const uint32_t kCR = 0x0A0D0A0Du, kSEP = 0x203A203Au;
+    const uint32_t k1 = 0x4C003C00u, k2 = 0x50004000u, k4 = 0x54004400u, k8 = 0x58004800u, kM = 0x64006400u;   // (1,16) (2,32) (4,64) (8,128) (1024,1024)
+#define SHL_H2(x) (*reinterpret_cast<const __half2*>(&(x)))
+    __half2 acc = __hfma2(__heq2(SHL_H2(sh), SHL_H2(kSEP)), SHL_H2(k1), SHL_H2(kM));
+    acc = __hfma2(__heq2(SHL_H2(sh), SHL_H2(kCR)), SHL_H2(k2), acc);
+    acc = __hfma2(__heq2(SHL_H2(w), SHL_H2(kSEP)), SHL_H2(k4), acc);
+    acc = __hfma2(__heq2(SHL_H2(w), SHL_H2(kCR)), SHL_H2(k8), acc);
+#undef SHL_H2
+    return *reinterpret_cast<const uint32_t*>(&acc) * 0x00010001u;
+}
+
 // ... of one 16-byte vector (c = the word before it): bit pair t <-> the byte pair that starts at byte t - 1
 __device__ __forceinline__ uint32_t vec_events(const uint32_t c, const uint4& v) {
+#if SHL_OPT_HGATHER
+    const uint32_t e0 = pair_events_h(c, v.x), e1 = pair_events_h(v.x, v.y), e2 = pair_events_h(v.y, v.z), e3 = pair_events_h(v.z, v.w);
+    return __byte_perm(__byte_perm(e0, e1, 0x0062), __byte_perm(e2, e3, 0x0062), 0x5410);     // byte 2 of each
+#else
     return (pair_events(c, v.x) & 0xffu) | ((pair_events(v.x, v.y) & 0xffu) << 8) |
            ((pair_events(v.y, v.z) & 0xffu) << 16) | (pair_events(v.z, v.w) << 24);
+#endif
 }
 
 // Running state of one lane's scan.  Events are only LISTED here (positions of the CR of every
@@ -368,27 +394,32 @@ __device__ __forceinline__ bool group_list_events(const uint8_t* A0, const uint3
         prev_last = __shfl_sync(SHL_FULL, vb.w, 31);
         const uint32_t ev0 = vec_events(c, va), ev1 = vec_events(va.w, vb);
         uint32_t cb0 = ev0 & 0xaaaaaaaau, sb0 = ev0 & 0x55555555u, cb1 = ev1 & 0xaaaaaaaau, sb1 = ev1 & 0x55555555u;
-        const uint32_t cnt = (uint32_t)(__popc(cb0) + __popc(cb1)) | ((uint32_t)(__popc(sb0) + __popc(sb1)) << 16);
+        const uint32_t n0c = (uint32_t)__popc(cb0), n0s = (uint32_t)__popc(sb0);
+        const uint32_t cnt = (n0c + (uint32_t)__popc(cb1)) | ((n0s + (uint32_t)__popc(sb1)) << 16);
         uint32_t inc = cnt;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(SHL_FULL, inc, d); if (lane >= d) inc += t; }
         const uint32_t tot = __shfl_sync(SHL_FULL, inc, 31);
         if (base_c + (tot & 0xffffu) > kCrFlat || base_s + (tot >> 16) > kSepFlat) { fits = false; break; }
-        uint32_t ic = base_c + ((inc - cnt) & 0xffffu), is = base_s + ((inc - cnt) >> 16);
+        // my slots: the first vector's events, then the second's
+        uint32_t ic0 = base_c + ((inc - cnt) & 0xffffu), is0 = base_s + ((inc - cnt) >> 16);
+        uint32_t ic1 = ic0 + n0c, is1 = is0 + n0s;
         const uint32_t q0 = boff - 1u, q1 = boff + 15u;
-        // a 16-byte vector rarely holds more than one event of a kind: the first of each is written by
-        // straight-line predicated code, the loops only run for what is left (CRLFCRLF, short lines)
-        if (cb0) { const int b = __ffs(cb0) - 1; cb0 &= cb0 - 1u; crl[ic++] = (uint16_t)(q0 + (uint32_t)(b >> 1)); }
-        if (sb0) { const int b = __ffs(sb0) - 1; sb0 &= sb0 - 1u; sepl[is++] = (uint16_t)(q0 + (uint32_t)(b >> 1)); }
-        if (cb0 | sb0) {
-            while (cb0) { const int b = __ffs(cb0) - 1; cb0 &= cb0 - 1u; crl[ic++] = (uint16_t)(q0 + (uint32_t)(b >> 1)); }
-            while (sb0) { const int b = __ffs(sb0) - 1; sb0 &= sb0 - 1u; sepl[is++] = (uint16_t)(q0 + (uint32_t)(b >> 1)); }
-        }
-        if (cb1) { const int b = __ffs(cb1) - 1; cb1 &= cb1 - 1u; crl[ic++] = (uint16_t)(q1 + (uint32_t)(b >> 1)); }
-        if (sb1) { const int b = __ffs(sb1) - 1; sb1 &= sb1 - 1u; sepl[is++] = (uint16_t)(q1 + (uint32_t)(b >> 1)); }
-        if (cb1 | sb1) {
-            while (cb1) { const int b = __ffs(cb1) - 1; cb1 &= cb1 - 1u; crl[ic++] = (uint16_t)(q1 + (uint32_t)(b >> 1)); }
-            while (sb1) { const int b = __ffs(sb1) - 1; sb1 &= sb1 - 1u; sepl[is++] = (uint16_t)(q1 + (uint32_t)(b >> 1)); }
+        // A vector rarely holds more than one event of a kind: the first of each kind is written
+        // without a branch (a lane with none writes to the spare slot behind the list), and one
+        // test covers what is left (the second CRLF of a CRLFCRLF, short lines).
+#define SHL_PUT_FIRST(bits, list, spare, idx, q) { const int b_ = __ffs(bits) - 1; const bool h_ = (bits) != 0u; \
+            (list)[h_ ? (idx) : (spare)] = (uint16_t)((q) + (uint32_t)(b_ >> 1)); (idx) += h_ ? 1u : 0u; (bits) &= (bits) - 1u; }
+        SHL_PUT_FIRST(cb0, crl, kCrFlat, ic0, q0)
+        SHL_PUT_FIRST(cb1, crl, kCrFlat, ic1, q1)
+        SHL_PUT_FIRST(sb0, sepl, kSepFlat, is0, q0)
+        SHL_PUT_FIRST(sb1, sepl, kSepFlat, is1, q1)
+#undef SHL_PUT_FIRST
+        if (cb0 | cb1 | sb0 | sb1) {
+            while (cb0) { const int b = __ffs(cb0) - 1; cb0 &= cb0 - 1u; crl[ic0++] = (uint16_t)(q0 + (uint32_t)(b >> 1)); }
+            while (cb1) { const int b = __ffs(cb1) - 1; cb1 &= cb1 - 1u; crl[ic1++] = (uint16_t)(q1 + (uint32_t)(b >> 1)); }
+            while (sb0) { const int b = __ffs(sb0) - 1; sb0 &= sb0 - 1u; sepl[is0++] = (uint16_t)(q0 + (uint32_t)(b >> 1)); }
+            while (sb1) { const int b = __ffs(sb1) - 1; sb1 &= sb1 - 1u; sepl[is1++] = (uint16_t)(q1 + (uint32_t)(b >> 1)); }
         }
         base_c += tot & 0xffffu; base_s += tot >> 16;
         va = na; vb = nb;
@@ -487,8 +518,8 @@ __device__ __noinline__ int find_term_scalar(const uint8_t* m, int from, int L) 
 // ----------------------------------------------------------------------------------- kernel
 template <bool kPlace>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_route(const RouteArgs a) {
-    __shared__ uint16_t s_cr[kWarpsPerBlock][kCrCap * 32];
-    __shared__ uint16_t s_sp[kWarpsPerBlock][kSepCap * 32];
+    __shared__ uint16_t s_cr[kWarpsPerBlock][kCrCap * 32 + 2];       // + a spare slot for branch-free writes
+    __shared__ uint16_t s_sp[kWarpsPerBlock][kSepCap * 32 + 2];
     __shared__ uint32_t s_codes[64];
     extern __shared__ uint32_t s_hist[];                       // kPlace: n_hosts bins (when they fit)
 
