@@ -460,18 +460,34 @@ __device__ __forceinline__ void group_walk(const uint16_t* crl, const uint16_t* 
     o.idx = (int)(prev - s0); o.n_c = 1u;
     while (js < n_s_tot && (uint32_t)sepl[js] < prev) js++;            // ": " inside the first line are not separators
     o.js0 = js;
-    uint32_t cur = js < n_s_tot ? (uint32_t)sepl[js] : 0xffffffffu;
+    // Line i (i = 0, 1, ...) must own separator js + i and no other: the loop only ANDs "it lies
+    // inside the line" (a second ": " in a line shows up as the next line's separator lying before
+    // that line); which line is the offender is worked out afterwards, in the rare bad block.
+    uint32_t ok = 1u;
+    const uint32_t ic0 = k;
     for (k++; k < n_c_tot; k++) {
         const uint32_t pos = crl[k];
         if (pos > lim) break;
         if (pos == prev + 2u && o.n_c >= 2u) { o.T = (int)(prev - s0); break; }       // empty line after the first line: CRLFCRLF
-        if (o.first_bad == 0xffffffffu) {                               // the line [prev + 2, pos) must hold exactly one ": "
-            const uint32_t nxt = js + 1u < n_s_tot ? (uint32_t)sepl[js + 1u] : 0xffffffffu;
-            if (cur > pos) { o.first_bad = o.n_c - 1u; o.err = SHL_E_HDR_NO_SEP; }
-            else if (nxt < pos) { o.first_bad = o.n_c - 1u; o.err = SHL_E_HDR_MULTI_SEP; }
-            else { cur = nxt; js++; }
-        }
+        const uint32_t si = js + o.n_c - 1u;
+        const uint32_t sv = si < n_s_tot ? (uint32_t)sepl[si] : 0xffffffffu;
+        ok &= (sv > prev ? 1u : 0u) & (sv < pos ? 1u : 0u);
         prev = pos; o.n_c++;
+    }
+    if (o.T < 0) return;
+    {
+        const uint32_t si = js + o.n_c - 1u;                            // the one after the last line's: beyond the block, or absent
+        const uint32_t sv = si < n_s_tot ? (uint32_t)sepl[si] : 0xffffffffu;
+        ok &= sv > prev ? 1u : 0u;
+    }
+    if (ok) return;
+    uint32_t cur = js < n_s_tot ? (uint32_t)sepl[js] : 0xffffffffu;
+    for (uint32_t line = 0; line + 1u < o.n_c; line++) {
+        const uint32_t end = crl[ic0 + line + 1u];
+        const uint32_t nxt = js + 1u < n_s_tot ? (uint32_t)sepl[js + 1u] : 0xffffffffu;
+        if (cur > end) { o.first_bad = line; o.err = SHL_E_HDR_NO_SEP; return; }
+        if (nxt < end) { o.first_bad = line; o.err = SHL_E_HDR_MULTI_SEP; return; }
+        cur = nxt; js++;
     }
 }
 
@@ -661,7 +677,9 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
                         sepv[j] = endv[j] = 0; c0v[j] = c1v[j] = 'x';
                         if (k0 + j < nh) {
                             sepv[j] = (int)spp[(k0 + j) * lstride] - lsub; endv[j] = (int)crp[(k0 + j + 1) * lstride] - lsub;
+#ifndef SHL_EXP_NOPEEK
                             if (sepv[j] + 2 < endv[j]) { c0v[j] = ldb(m + sepv[j] + 2); c1v[j] = ldb(m + endv[j] - 1); }
+#endif
                         }
                     }
 #pragma unroll
