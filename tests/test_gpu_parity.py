@@ -283,6 +283,32 @@ def test_structural_edge_cases(eng):
     assert_frame_equal(ar, eng.frame(ar, g, reuse_arena=True), O.orc_frame(ar, o), 'edge frame')
 
 
+def test_token_soup_through_the_span_scan(eng):
+    """Groups of small messages are scanned as one span of bytes: random sequences of the tokens
+    the grammar is made of (so that CRLFs, ': ', spaces and their halves land next to message
+    boundaries, list slices and row edges in every combination), tightly packed and with gaps."""
+    rng = np.random.default_rng(11)
+    toks = [b'\r\n', b'\r\n', b': ', b': ', b' ', b':', b'\r', b'\n', b'\t', b'a', b'bc', b'Host', b'GET', b'POST', b'/x/y',
+            b'HTTP/1.1', b'HTTP/1.0', b'HTTP/2', b'200', b'OK', b'Content-Length', b'content-length', b'5', b'-1', b'1e3',
+            b'Transfer-Encoding', b'chunked', b'\r\n\r\n', b'\x00', b'\xff', b'\x0b']
+    msgs = []
+    for i in range(6000):
+        k = int(rng.integers(0, 40))
+        m = b''.join(toks[j] for j in rng.integers(0, len(toks), k))
+        if i % 3 == 0:                                    # a well-formed skeleton with soup in the values
+            hdrs = b''.join(b'K%d: %s\r\n' % (h, b''.join(toks[j] for j in rng.integers(2, len(toks), int(rng.integers(0, 4)))).replace(b'\r\n', b'_'))
+                            for h in range(int(rng.integers(0, 12))))
+            m = b'GET /' + m.replace(b' ', b'').replace(b'\r', b'').replace(b'\n', b'')[:40] + b' HTTP/1.1\r\n' + hdrs + b'\r\n'
+        msgs.append(m)
+    for name, ar in (('tight', eng.pack(msgs)), ('gaps', scatter_pack(eng, msgs, rng))):
+        g, o = eng.parse(ar), O.orc_parse(ar)
+        assert_parse_equal(ar, g, o, 'token soup ' + name)
+        assert_frame_equal(ar, eng.frame(ar, g, reuse_arena=True), O.orc_frame(ar, o), 'token soup frame ' + name)
+    # every outcome the tokeniser knows shows up in this corpus
+    seen = set(int(c) for c in np.unique(o.status[:ar.n] & 0xff))
+    assert {N.S_OK, N.S_INCOMPLETE_LINE, N.S_INCOMPLETE_HEADERS, N.E_FIRSTLINE_PARTS, N.E_HDR_NO_SEP, N.E_HDR_MULTI_SEP} <= seen, seen
+
+
 def test_empty_and_tiny_batches(eng):
     for msgs in ([b''], [b'', b'', b''], [b'G'], [b'\r\n'], [b'GET / HTTP/1.1\r\nA: b\r\n\r\n'] * 33):
         ar = eng.pack(msgs)
