@@ -4,39 +4,38 @@
 // decision (/root/reference/src/python/shellac/server/HttpParser.py:140-223, 304-337), driven
 // over a whole message as the reference's own test loop does (test/HttpParserTests.py:36-39).
 //
-// Mapping (round 1, third design; profiles/r01/ has the ncu summaries of the earlier ones: a warp
-// per message with ballot/shuffle structure extraction ran 960 warp-instructions per request, a
-// lane per message that handled every line end inside the scan loop ran 406): one warp owns a
-// GROUP of 32 consecutive messages, LANE j owns MESSAGE j.
-//   scan     each lane streams its own message in 32-byte sectors (aligned down, lead bytes
-//            masked, next sector in flight), classifies the bytes with SWAR compares (CR, LF,
-//            ':', ' ') into 16-bit masks "LF preceded by CR" / "' ' preceded by ':'" (the previous
-//            vector's last-byte flags ride in two registers) and does nothing with the set bits
-//            but append their positions to two lane-private, lane-interleaved u16 lists in
-//            shared memory; two consecutive CRLFs after the first line end the scan.  The loop
-//            body that runs under divergence is a dozen instructions.
-//            The same loop notes the first two spaces while on the first line and checks, as
-//            CRLFs arrive, that each header line held exactly one ": ".
-//   epilogue lanes are converged again: first-line evaluation, one atomic record allocation per group, value
-//            strip + record write, Content-Length / Transfer-Encoding decision, struct-of-arrays
-//            stores (lane j == message j, so they are coalesced), MD5 + continuum search +
-//            shared-memory histogram.
-// Anything off the canonical shape (responses' first line, whitespace around the header block,
-// more lines than the lists hold) takes a per-lane scalar path with the same semantics.
+// Mapping (round 1, fifth design; DESIGN.md section 4 and profiles/r01/ have the history: a warp
+// per message ran 960 warp-instructions per request, a lane per message 340, this one 277): one
+// warp owns a GROUP of 32 consecutive messages.
+//   phase A  the group's messages normally lie back to back, so the warp scans ONE span of bytes:
+//            lane l classifies 32 bytes of every 1 KiB row (coalesced, next row in flight) for the
+//            byte pairs "\r\n" and ": " (fp16x2 compares + HFMA2 gather, see pair_events_h) and
+//            the set bits are compacted, in position order, into two flat u16 lists per group
+//            with one warp prefix sum per row (group_list_events);
+//   phase B  lane j == message j: binary search for the message's slice of the lists, walk its
+//            CRLFs: first line end, CRLFCRLF, exactly one ": " per line (group_walk);
+//   epilogue lane j == message j: first-line evaluation, one atomic record allocation per group,
+//            value strip + record write, Content-Length / Transfer-Encoding decision,
+//            struct-of-arrays stores (coalesced), MD5 + continuum search + shared-memory histogram.
+// A group that is not a span (unordered or overlapping messages, bodies, too many events) is
+// scanned message-per-lane (scan_lists) into lane-interleaved lists, same epilogue.  Anything off
+// the canonical shape (responses' first line, whitespace around the header block, more lines than
+// the per-lane lists hold) takes a per-lane scalar path with the same semantics.
 #pragma once
 #include <cuda_fp16.h>
 #include "shl_device.cuh"
 
 namespace shl {
 
+// build-time switches kept for A/B timing (tools/build_variants.py)
 #ifndef SHL_OPT_RINGDIR
-#define SHL_OPT_RINGDIR 1
+#define SHL_OPT_RINGDIR 1             // continuum search through the 4 096-bucket directory
 #endif
 #ifndef SHL_OPT_MINBLOCKS
-#define SHL_OPT_MINBLOCKS 8
+#define SHL_OPT_MINBLOCKS 8           // resident blocks per SM the register allocation aims at
 #endif
 #ifndef SHL_OPT_BATCH
-#define SHL_OPT_BATCH 2
+#define SHL_OPT_BATCH 2               // header lines whose value peeks are in flight together
 #endif
 constexpr int kWarpsPerBlock = 4;
 constexpr int kGroup = 32;            // messages per warp (one per lane)
