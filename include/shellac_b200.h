@@ -233,6 +233,10 @@ int  shl_group_dev(shl_ctx* ctx, const uint32_t* d_node, uint64_t n, uint32_t n_
 /* ------------------------------------------------------------------------------------------
  * Device-resident entry points: same semantics, every data pointer is a DEVICE pointer and no
  * copy is made.  For callers whose arenas already live in HBM, and for kernel-only timing.
+ * d_arena must be 32-byte aligned (SHL_ERR_ARG otherwise) and followed by 64 readable bytes: the
+ * kernels read whole 32-byte sectors around a message (cudaMalloc'd buffers from
+ * shl_device_alloc(bytes + 64) qualify).  Messages may be indexed in any order and may overlap;
+ * groups of 32 consecutive messages that lie in index order are scanned fastest.
  * ---------------------------------------------------------------------------------------- */
 int  shl_parse_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_off, const uint32_t* d_len,
                    uint64_t n, const shl_parse_out* d_out);
