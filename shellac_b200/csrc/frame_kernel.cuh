@@ -59,17 +59,54 @@ struct FrameArgs {
     shl_frame_out out;
 };
 
+// The common chunk header, [CRLF] 1-8 hex digits CRLF, matched and converted from ONE 16-byte
+// window held in registers (three independent aligned loads, so a chunk costs one memory round
+// trip instead of a dozen dependent byte loads; the walk is a pointer chase and nothing else).
+// true: *idx = match length, *size = int(digits, 16).  false: not this shape (extension,
+// longer run, "0x" prefix, bad digit, no match, window past the message) - the caller then runs
+// the byte-wise restatement of the regex, which decides.
+__device__ __forceinline__ bool chunk_header_fast(const uint8_t* m, int64_t p, int64_t L, int64_t* idx, unsigned long long* size) {
+    if (p + 16 > L) return false;
+    const uint8_t* s = m + p;
+    const unsigned long long* q = reinterpret_cast<const unsigned long long*>(reinterpret_cast<uintptr_t>(s) & ~(uintptr_t)7);
+    const int sh = (int)(reinterpret_cast<uintptr_t>(s) & 7) * 8;
+    const unsigned long long q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2);
+    unsigned long long lo = sh ? (q0 >> sh) | (q1 << (64 - sh)) : q0;      // bytes 0..7 of the window
+    unsigned long long hi = sh ? (q1 >> sh) | (q2 << (64 - sh)) : q1;      // bytes 8..15
+    int used = 0;
+    if ((lo & 0xffffull) == 0x0a0dull) {                                    // optional leading CRLF
+        lo = (lo >> 16) | (hi << 48); hi >>= 16; used = 2;
+    }
+    unsigned long long acc = 0; int nd = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        const uint32_t c = (uint32_t)(lo >> (8 * k)) & 0xffu;
+        const int h = hexval(c);
+        if (nd == k) { if (h >= 0) { acc = acc * 16ull + (unsigned long long)h; nd = k + 1; } }
+    }
+    if (nd == 0) return false;
+    // the two bytes after the run: CRLF, else something the exact matcher has to look at
+    const unsigned long long tail = nd == 8 ? hi : (lo >> (8 * nd)) | (hi << (64 - 8 * nd));
+    if ((tail & 0xffffull) != 0x0a0dull) return false;
+    if (nd >= 2 && (lo & 0xffull) == '0' && ((lo >> 8) & 0xdfull) == 'X') return false;   // "0x..." cannot be: 'x' is not hex; kept for clarity
+    *idx = used + nd + 2; *size = acc;
+    return true;
+}
+
 struct Walk { uint32_t fs, nch, last; int64_t end; unsigned long long bytes; };
 
 template <bool kEmit>
 __device__ __forceinline__ Walk walk_chunks(const uint8_t* m, int64_t L, int64_t p, shl_chunk_span* dst, uint32_t cap) {
     Walk w; w.fs = SHL_S_INCOMPLETE_BODY; w.nch = 0; w.last = 0; w.bytes = 0;
     while (p < L) {
-        int64_t a, b;
-        const int64_t idx = chunk_header_match(m, p, L, a, b);
-        if (idx < 0) { w.last = (uint32_t)(L - p); p = L; break; }                 // :255-256
+        int64_t idx;
         unsigned long long size;
-        if (!py_int16(m + a, b - a, size)) { w.fs = SHL_E_CHUNK_HEX; break; }       // :239-241
+        if (!chunk_header_fast(m, p, L, &idx, &size)) {
+            int64_t a, b;
+            idx = chunk_header_match(m, p, L, a, b);
+            if (idx < 0) { w.last = (uint32_t)(L - p); p = L; break; }             // :255-256
+            if (!py_int16(m + a, b - a, size)) { w.fs = SHL_E_CHUNK_HEX; break; }   // :239-241
+        }
         const int64_t left = L - (p + idx);
         if (size == 0ull) {                                                          // :268-287
             if (left >= 2 && ldb(m + p + idx) == '\r' && ldb(m + p + idx + 1) == '\n') {
