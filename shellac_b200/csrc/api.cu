@@ -35,6 +35,7 @@ struct shl_ctx {
     uint8_t* d_arena = nullptr; uint64_t* d_off = nullptr; uint32_t* d_len = nullptr;
     uint64_t* d_koff = nullptr; uint32_t* d_klen = nullptr;
     shl_parse_out dp{}; shl_frame_out df{}; shl_place_out dq{};
+    shl_parse_out cur_dp{};               // where the LAST *_batch parse left its per-message fields (dp, or the small-batch block)
     uint64_t* d_counters = nullptr;       // [0]=hdr_used [1]=chunk_used [2..66)=code_hist
     uint64_t* h_counters = nullptr;       // pinned mirror
     int32_t* d_ch_len = nullptr; uint64_t* d_ch_size = nullptr; uint8_t* d_ch_ok = nullptr;
@@ -54,6 +55,11 @@ struct shl_ctx {
     uint64_t* d_chunk_used = nullptr;     // [kMaxChunks]
     uint64_t* h_chunk_used = nullptr;     // pinned mirror
     int pipeline = 1;                     // SHL_PIPELINE=0 disables the chunked path
+    // small-batch path (one reactor tick): every result of a call lands in ONE device block that
+    // comes back with ONE copy into a pinned mirror, and is handed out from there on the host
+    static constexpr uint64_t kSmallMsgs = 8192;
+    uint8_t* d_small = nullptr; uint8_t* h_small = nullptr; uint64_t small_bytes = 0;
+    int small_path = 1;                   // SHL_SMALL=0 disables it
     std::string err;
 };
 
@@ -172,6 +178,7 @@ int shl_ctx_create(int device, uint64_t max_msgs, uint64_t max_bytes, uint64_t m
     CU(cudaMalloc(&blk, parse_block_bytes(n)));
     shl_hdr_span* hdr = nullptr; CU(dalloc(&hdr, ctx->max_records));
     ctx->dp = slice_parse(blk, n, hdr, ctx->max_records, ctx->d_counters + 0);
+    ctx->cur_dp = ctx->dp;
     shl_frame_out& f = ctx->df;
     CU(dalloc(&f.fstatus, n)); CU(dalloc(&f.n_chunks, n)); CU(dalloc(&f.chunk_base, n));
     CU(dalloc(&f.body_end, n)); CU(dalloc(&f.body_bytes, n)); CU(dalloc(&f.last_call, n));
@@ -188,6 +195,7 @@ int shl_ctx_create(int device, uint64_t max_msgs, uint64_t max_bytes, uint64_t m
     CU(dalloc(&ctx->d_chunk_used, shl_ctx::kMaxChunks));
     CU(cudaHostAlloc(reinterpret_cast<void**>(&ctx->h_chunk_used), shl_ctx::kMaxChunks * sizeof(uint64_t), cudaHostAllocDefault));
     { const char* pl = getenv("SHL_PIPELINE"); if (pl && pl[0] == '0') ctx->pipeline = 0; }
+    { const char* sm = getenv("SHL_SMALL"); if (sm && sm[0] == '0') ctx->small_path = 0; }
     const char* fs = getenv("SHL_FORCE_SCALAR");
     ctx->force_scalar = (fs && fs[0] == '1') ? 1 : 0;
     *out = ctx;
@@ -214,6 +222,7 @@ void shl_ctx_destroy(shl_ctx* ctx) {
     for (auto& e : ctx->ev_join) cudaEventDestroy(e);
     for (auto& e : ctx->ev_chunk) cudaEventDestroy(e);
     cudaFree(ctx->d_chunk_used); cudaFreeHost(ctx->h_chunk_used);
+    cudaFree(ctx->d_small); if (ctx->h_small) cudaFreeHost(ctx->h_small);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -467,6 +476,85 @@ static int place_out_d2h(shl_ctx* ctx, const shl_place_out* out, uint64_t n) {
     return SHL_OK;
 }
 
+// ---- small batches: one block out, one copy back ---------------------------------------------------
+// A reactor tick hands over a few hundred messages.  Bringing their results back field by field
+// costs some twenty cudaMemcpyAsync calls and three stream syncs (~115 us a call whatever the
+// size); here the kernel writes every field into one device block laid out for this n, one D2H
+// brings the block to a pinned mirror, and the fields are copied out to the caller's arrays on
+// the host.  Returns 1 when the call does not qualify (the general path then runs).
+struct SmallLayout {
+    uint64_t content_len, md5, u32[10], hash, node, used, hist, rec, rec_cap, total;
+};
+static SmallLayout small_layout(uint64_t n, uint32_t n_hosts) {
+    SmallLayout l{}; uint64_t o = 0;
+    l.md5 = o; o += 16 * n;                                  // 16-byte stores: keep it first (the block is 256-byte aligned)
+    l.content_len = o; o += 8 * n;
+    for (int k = 0; k < 10; k++) { l.u32[k] = o; o += 4 * n; }
+    l.hash = o; o += 4 * n;
+    l.node = o; o += 4 * n;
+    o = (o + 7) & ~7ull;
+    l.used = o; o += 8;
+    l.hist = o; o += 8ull * n_hosts;
+    l.rec = o; l.rec_cap = 24 * n + 64; o += 8 * l.rec_cap;
+    l.total = o;
+    return l;
+}
+static int route_small(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, const uint64_t* off, const uint32_t* len,
+                       uint64_t n, const shl_parse_out* pout, const shl_place_out* qout) {
+    if (!ctx->small_path || !arena || n == 0 || n > shl_ctx::kSmallMsgs) return 1;
+    const uint32_t nh = qout ? ctx->n_hosts : 0u;
+    const SmallLayout l = small_layout(n, nh);
+    if (!ctx->d_small) {
+        const SmallLayout big = small_layout(shl_ctx::kSmallMsgs, 65536);
+        CU(cudaMalloc(reinterpret_cast<void**>(&ctx->d_small), big.total));
+        CU(cudaHostAlloc(reinterpret_cast<void**>(&ctx->h_small), big.total, cudaHostAllocDefault));
+        ctx->small_bytes = big.total;
+    }
+    if (l.total > ctx->small_bytes) return 1;
+    if (int rc = stage_in(ctx, arena, arena_bytes, off, len, n, ctx->d_off, ctx->d_len)) return rc;
+    uint8_t* d = ctx->d_small;
+    CU(cudaMemsetAsync(d + l.used, 0, 8 + 8ull * nh, ctx->stream));
+    shl_parse_out o{};
+    o.content_len = reinterpret_cast<int64_t*>(d + l.content_len);
+    o.status = reinterpret_cast<uint32_t*>(d + l.u32[0]); o.first_line_len = reinterpret_cast<uint32_t*>(d + l.u32[1]);
+    o.headers_len = reinterpret_cast<uint32_t*>(d + l.u32[2]); o.sp1 = reinterpret_cast<uint32_t*>(d + l.u32[3]);
+    o.sp2 = reinterpret_cast<uint32_t*>(d + l.u32[4]); o.fl_end = reinterpret_cast<uint32_t*>(d + l.u32[5]);
+    o.slash = reinterpret_cast<uint32_t*>(d + l.u32[6]); o.status_code = reinterpret_cast<int32_t*>(d + l.u32[7]);
+    o.n_headers = reinterpret_cast<uint32_t*>(d + l.u32[8]); o.hdr_base = reinterpret_cast<uint32_t*>(d + l.u32[9]);
+    o.hdr = reinterpret_cast<shl_hdr_span*>(d + l.rec); o.hdr_cap = l.rec_cap; o.hdr_used = reinterpret_cast<uint64_t*>(d + l.used);
+    shl_place_out q{};
+    if (qout) {
+        q.md5 = d + l.md5; q.hash = reinterpret_cast<uint32_t*>(d + l.hash); q.node = reinterpret_cast<uint32_t*>(d + l.node);
+        q.hist = qout->hist ? reinterpret_cast<uint64_t*>(d + l.hist) : nullptr;
+    }
+    ctx->cur_dp = o;
+    if (int rc = launch_route(ctx, ctx->d_arena, ctx->d_off, ctx->d_len, n, &o, qout ? &q : nullptr)) return rc;
+    CU(cudaMemcpyAsync(ctx->h_small, d, l.total, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    const uint8_t* h = ctx->h_small;
+    const uint64_t used = *reinterpret_cast<const uint64_t*>(h + l.used);
+    if (used > l.rec_cap) return 1;                       // more records than the block holds: the general path decides
+    if (pout->hdr && used > pout->hdr_cap)
+        return fail(ctx, SHL_ERR_CAPACITY, "header record arena overflowed: raise max_records / hdr_cap");
+#define OUT(dst, src_off, bytes) do { if (dst) std::memcpy((dst), h + (src_off), (bytes)); } while (0)
+    OUT(pout->content_len, l.content_len, 8 * n);
+    OUT(pout->status, l.u32[0], 4 * n); OUT(pout->first_line_len, l.u32[1], 4 * n); OUT(pout->headers_len, l.u32[2], 4 * n);
+    OUT(pout->sp1, l.u32[3], 4 * n); OUT(pout->sp2, l.u32[4], 4 * n); OUT(pout->fl_end, l.u32[5], 4 * n);
+    OUT(pout->slash, l.u32[6], 4 * n); OUT(pout->status_code, l.u32[7], 4 * n); OUT(pout->n_headers, l.u32[8], 4 * n);
+    OUT(pout->hdr_base, l.u32[9], 4 * n);
+    OUT(pout->hdr, l.rec, 8 * used);
+    if (pout->hdr_used) *pout->hdr_used = used;
+    if (qout) {
+        OUT(qout->md5, l.md5, 16 * n); OUT(qout->hash, l.hash, 4 * n); OUT(qout->node, l.node, 4 * n);
+        if (qout->hist) {                                   // `hist` is ADDED to
+            const uint64_t* bins = reinterpret_cast<const uint64_t*>(h + l.hist);
+            for (uint32_t i = 0; i < nh; i++) qout->hist[i] += bins[i];
+        }
+    }
+#undef OUT
+    return SHL_OK;
+}
+
 // ---- chunked, multi-stream version of parse/route for large batches -----------------------------
 // The batch is cut into message ranges; chunk c runs H2D(arena slice, index slice) -> kernel ->
 // D2H(result slices) on stream c % kPipe, so the copy engines of both directions and the SMs are
@@ -478,6 +566,7 @@ static int route_pipelined(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_by
                            uint64_t n, const shl_parse_out* pout, const shl_place_out* qout) {
     constexpr int kPipe = shl_ctx::kPipe, kMaxChunks = shl_ctx::kMaxChunks;
     if (!ctx->pipeline || !arena || n < 65536) return 1;
+    ctx->cur_dp = ctx->dp;
     const int nch = (int)std::min<uint64_t>(kMaxChunks, std::max<uint64_t>(2, n / 65536));
     const uint64_t per = ((n + nch - 1) / nch + 31) & ~31ull;
     // cheap density probe (the exact byte range of a chunk is computed right before it is queued,
@@ -558,11 +647,14 @@ int shl_parse_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, co
     if (!out) return fail(ctx, SHL_ERR_ARG, "out is null");
     if (ctx && off && len && n <= ctx->max_msgs && arena_bytes <= ctx->max_bytes) {
         CU(cudaSetDevice(ctx->device));
-        const int rc = route_pipelined(ctx, arena, arena_bytes, off, len, n, out, nullptr);
+        int rc = route_small(ctx, arena, arena_bytes, off, len, n, out, nullptr);
+        if (rc <= 0) return rc;
+        rc = route_pipelined(ctx, arena, arena_bytes, off, len, n, out, nullptr);
         if (rc <= 0) return rc;
     }
     if (int rc = stage_in(ctx, arena, arena_bytes, off, len, n, ctx->d_off, ctx->d_len)) return rc;
     CU(cudaMemsetAsync(ctx->d_counters, 0, 8, ctx->stream));
+    ctx->cur_dp = ctx->dp;
     if (int rc = shl_parse_dev(ctx, ctx->d_arena, ctx->d_off, ctx->d_len, n, &ctx->dp)) return rc;
     return parse_out_d2h(ctx, out, n);
 }
@@ -573,7 +665,9 @@ int shl_route_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, co
     if (ctx && !ctx->d_ring_values) return fail(ctx, SHL_ERR_NO_RING, "shl_ring_build() has not been called");
     if (ctx && off && len && n <= ctx->max_msgs && arena_bytes <= ctx->max_bytes) {
         CU(cudaSetDevice(ctx->device));
-        const int rc = route_pipelined(ctx, arena, arena_bytes, off, len, n, pout, qout);
+        int rc = route_small(ctx, arena, arena_bytes, off, len, n, pout, qout);
+        if (rc <= 0) return rc;
+        rc = route_pipelined(ctx, arena, arena_bytes, off, len, n, pout, qout);
         if (rc <= 0) return rc;
     }
     if (int rc = stage_in(ctx, arena, arena_bytes, off, len, n, ctx->d_off, ctx->d_len)) return rc;
@@ -581,6 +675,7 @@ int shl_route_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, co
     shl_place_out dq = ctx->dq;
     dq.hist = qout->hist ? ctx->d_hist : nullptr;
     if (dq.hist) CU(cudaMemsetAsync(ctx->d_hist, 0, (size_t)ctx->n_hosts * 8, ctx->stream));
+    ctx->cur_dp = ctx->dp;
     if (int rc = shl_route_dev(ctx, ctx->d_arena, ctx->d_off, ctx->d_len, n, &ctx->dp, &dq)) return rc;
     if (int rc = parse_out_d2h(ctx, pout, n)) return rc;
     return place_out_d2h(ctx, qout, n);
@@ -604,12 +699,14 @@ int shl_frame_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, co
     if (!out || !status || !first_line_len || !headers_len) return fail(ctx, SHL_ERR_ARG, "null pointer");
     if (int rc = stage_in(ctx, arena, arena_bytes, off, len, n, ctx->d_off, ctx->d_len)) return rc;
     // the parse fields travel with the call so it can be used on its own (they are tiny next to the arena)
-    CU(cudaMemcpyAsync(ctx->dp.status, status, n * 4, cudaMemcpyHostToDevice, ctx->stream));
-    CU(cudaMemcpyAsync(ctx->dp.first_line_len, first_line_len, n * 4, cudaMemcpyHostToDevice, ctx->stream));
-    CU(cudaMemcpyAsync(ctx->dp.headers_len, headers_len, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    if (n > shl_ctx::kSmallMsgs) ctx->cur_dp = ctx->dp;    // cannot be the continuation of a small-batch parse
+    const shl_parse_out& cur = ctx->cur_dp;
+    CU(cudaMemcpyAsync(cur.status, status, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(cur.first_line_len, first_line_len, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(cur.headers_len, headers_len, n * 4, cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaMemsetAsync(ctx->d_counters + 1, 0, 8, ctx->stream));
-    if (int rc = shl_frame_dev(ctx, ctx->d_arena, ctx->d_off, ctx->d_len, n, ctx->dp.status, ctx->dp.first_line_len,
-                               ctx->dp.headers_len, &ctx->df)) return rc;
+    if (int rc = shl_frame_dev(ctx, ctx->d_arena, ctx->d_off, ctx->d_len, n, cur.status, cur.first_line_len,
+                               cur.headers_len, &ctx->df)) return rc;
     const shl_frame_out& d = ctx->df;
     D2H(out->fstatus, d.fstatus, n * 4); D2H(out->n_chunks, d.n_chunks, n * 4); D2H(out->chunk_base, d.chunk_base, n * 4);
     D2H(out->body_end, d.body_end, n * 8); D2H(out->body_bytes, d.body_bytes, n * 8); D2H(out->last_call, d.last_call, n * 4);
@@ -656,7 +753,7 @@ int shl_body_batch(shl_ctx* ctx, uint64_t n, const shl_body_out* out) {
     d.body_cap = std::min<uint64_t>(ctx->max_bytes + 16 * ctx->max_msgs, out->body ? out->body_cap : ~0ull);
     d.body_used = ctx->d_counters + 1;                  // the frame pass is done with its counter
     CU(cudaMemsetAsync(ctx->d_counters + 1, 0, 8, ctx->stream));
-    if (int rc = shl_body_dev(ctx, ctx->d_arena, ctx->d_off, ctx->d_len, n, &ctx->dp, &ctx->df, &d)) return rc;
+    if (int rc = shl_body_dev(ctx, ctx->d_arena, ctx->d_off, ctx->d_len, n, &ctx->cur_dp, &ctx->df, &d)) return rc;
     D2H(out->body_off, d.body_off, n * 8); D2H(out->body_len, d.body_len, n * 8);
     CU(cudaMemcpyAsync(ctx->h_counters + 1, ctx->d_counters + 1, 8, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));

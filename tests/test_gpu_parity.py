@@ -182,6 +182,34 @@ def test_fresh_engines_give_the_same_records_every_time(golden):
             e.close()
 
 
+def test_host_paths_small_block_and_field_by_field_agree(golden, monkeypatch):
+    """Batches of up to 8 192 messages come back through one device block and one copy
+    (route_small in api.cu); SHL_SMALL=0 forces the field-by-field path the larger ones take.
+    Both against the oracle, including frame + body gather continuing from either."""
+    from shellac_b200.engine import Engine
+    msgs = [w['msg'] for w in golden['whole']]
+    hosts = ['10.0.0.%d' % (i + 1) for i in range(16)]
+    outs = []
+    for small in ('1', '0'):
+        monkeypatch.setenv('SHL_SMALL', small)
+        e = Engine(device=0, max_msgs=1 << 14, max_bytes=1 << 28, max_records=1 << 20)
+        try:
+            e.ring_build(hosts)
+            ar = e.pack(msgs)
+            po, qo = e.route(ar)
+            o = O.orc_parse(ar)
+            assert_parse_equal(ar, po, o, 'SHL_SMALL=' + small)
+            fo = e.frame(ar, po, reuse_arena=True)
+            of = O.orc_frame(ar, o)
+            assert_frame_equal(ar, fo, of, 'frame after SHL_SMALL=' + small)
+            bo, ob = e.body(ar), O.orc_body(ar, o, of)
+            assert (bo.body_len[:ar.n] == ob.body_len[:ar.n]).all()
+            outs.append((qo.node[:ar.n].copy(), qo.hash[:ar.n].copy(), qo.hist.copy()))
+        finally:
+            e.close()
+    assert (outs[0][0] == outs[1][0]).all() and (outs[0][1] == outs[1][1]).all() and (outs[0][2] == outs[1][2]).all()
+
+
 def test_golden_streams_and_gzip(eng, golden):
     for s in golden['streams']:
         data, start = s['stream'], 0
