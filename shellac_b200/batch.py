@@ -75,10 +75,14 @@ class ParseOut(object):
         self.hdr_used = alloc(1, np.uint64)
 
     def struct(self):
-        s = N.ParseOutStruct()
-        for name, _ in N.PARSE_FIELDS:
-            setattr(s, name, getattr(self, name).ctypes.data)
-        s.hdr, s.hdr_cap, s.hdr_used = self.hdr.ctypes.data, self.hdr_cap, self.hdr_used.ctypes.data
+        """The C struct of this object's array addresses (built once: the arrays never move)."""
+        s = getattr(self, '_struct', None)
+        if s is None:
+            s = N.ParseOutStruct()
+            for name, _ in N.PARSE_FIELDS:
+                setattr(s, name, getattr(self, name).ctypes.data)
+            s.hdr, s.hdr_cap, s.hdr_used = self.hdr.ctypes.data, self.hdr_cap, self.hdr_used.ctypes.data
+            self._struct = s
         return s
 
     def code(self):
@@ -128,10 +132,13 @@ class PlaceOut(object):
         self.hist = alloc(n_nodes, np.uint64) if n_nodes else None
 
     def struct(self):
-        s = N.PlaceOutStruct()
-        s.md5 = self.md5.ctypes.data if self.md5 is not None else None
-        s.hash, s.node = self.hash.ctypes.data, self.node.ctypes.data
-        s.hist = self.hist.ctypes.data if self.hist is not None else None
+        s = getattr(self, '_struct', None)
+        if s is None:
+            s = N.PlaceOutStruct()
+            s.md5 = self.md5.ctypes.data if self.md5 is not None else None
+            s.hash, s.node = self.hash.ctypes.data, self.node.ctypes.data
+            s.hist = self.hist.ctypes.data if self.hist is not None else None
+            self._struct = s
         return s
 
     def digest(self, i):

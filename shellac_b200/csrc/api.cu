@@ -376,7 +376,13 @@ static int launch_route(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_
     a.code_hist = ctx->d_counters + 2; a.force_scalar = ctx->force_scalar;
     a.k = shl::swar_host_consts();
     a.hdr_base_bias = bias;
-    const uint64_t groups = (n + shl::kGroup - 1) / shl::kGroup;
+    // a warp takes 32 messages when there are enough of them to fill the machine; a reactor-sized
+    // batch is spread over more warps (down to one message each) so that the kernel's critical
+    // path is one message's worth of rows, not thirty-two
+    uint32_t gsz = shl::kGroup;
+    while (gsz > 1 && n / gsz < 148ull * 8ull) gsz >>= 1;
+    a.group = gsz;
+    const uint64_t groups = (n + gsz - 1) / gsz;
     const unsigned blocks = (unsigned)((groups + shl::kWarpsPerBlock - 1) / shl::kWarpsPerBlock);
     if (d_q) {
         a.ring_values = ctx->d_ring_values; a.ring_nodes = ctx->d_ring_nodes; a.ring_dir = ctx->d_ring_dir;

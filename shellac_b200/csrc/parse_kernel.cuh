@@ -88,6 +88,7 @@ struct RouteArgs {
     int force_scalar;                 // test hook: take the scalar path for every message
     SwarK k;                          // SWAR byte constants, as run-time values (see SwarK)
     uint32_t hdr_base_bias;           // added to the stored hdr_base (out.hdr may be a slice of a larger arena)
+    uint32_t group;                   // messages per warp, 1..32 (small batches: fewer per warp, more warps, shorter chains)
     // fused placement (route); ring_values == nullptr -> parse only
     const uint32_t* ring_values; const uint32_t* ring_nodes; const uint32_t* ring_dir; uint32_t n_points, n_hosts;
     shl_place_out place;
@@ -548,8 +549,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
     // (A block-level counting sort of the messages by scan length, so that the lanes of a warp
     // finish together, was tried here: 1.6 % faster and one more thing to get wrong.  Not kept.)
     {
-        const uint64_t mine = ((uint64_t)blockIdx.x * kWarpsPerBlock + warp) * kGroup + lane;
-        const bool have = mine < a.n;
+        const uint64_t mine = ((uint64_t)blockIdx.x * kWarpsPerBlock + warp) * a.group + lane;
+        const bool have = (uint32_t)lane < a.group && mine < a.n;
         const uint64_t my_off = have ? a.off[mine] : 0ull;
         const int L = have ? (int)min(a.len[mine], 0x7fffffc0u) : 0;
         const uint8_t* m = a.arena + my_off;

@@ -26,3 +26,20 @@ for n in (1, 32, 256, 1024, 4096, 16384):
         ts.append(time.perf_counter() - t0)
     ts = np.array(ts) * 1e6
     print('n=%6d  median %.1f us  p90 %.1f us  -> %.2f M req/s' % (n, np.median(ts), np.percentile(ts, 90), n / np.median(ts)))
+
+# the same call without the Python wrapper's per-call work (structs built once)
+import ctypes as C
+n = 256
+ar = eng.corpus_host(20130725, 0, n, 0)
+pout = ParseOut(n, n * 24, alloc=eng.pinned)
+qout = PlaceOut(n, len(hosts), alloc=eng.pinned)
+ps, qs = pout.struct(), qout.struct()
+args = (eng.ctx, ar.data.ctypes.data, ar.nbytes + 64, ar.off.ctypes.data, ar.len.ctypes.data, n, C.byref(ps), C.byref(qs))
+for _ in range(50):
+    assert eng.lib.shl_route_batch(*args) == 0
+ts = []
+for _ in range(300):
+    t0 = time.perf_counter()
+    eng.lib.shl_route_batch(*args)
+    ts.append(time.perf_counter() - t0)
+print('n=%d bare C ABI call: median %.1f us' % (n, np.median(np.array(ts) * 1e6)))
