@@ -432,7 +432,7 @@ def run_ours(args):
                 'host_numa': 'process bound to NUMA node %d (%d cpus) of its GPU' % numa if numa else 'unbound',
                 'clocks': e_clocks},
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
-                     'traffic': ncu_traffic(), 'kernel': 'shl::k_route<true>', 'kernel_ms': k_ms,
+                     'traffic': ncu_traffic(), 'kernel': 'shl::k_route<true, true>', 'kernel_ms': k_ms,
                      'algorithmic_bytes_per_launch': alg_bytes, 'bytes_per_request': alg_bytes / n,
                      'peak_source': peak_src, 'frac_of_nominal_8TBs': achieved / 8000.0},
     }

@@ -186,8 +186,10 @@ int shl_ctx_create(int device, uint64_t max_msgs, uint64_t max_bytes, uint64_t m
     shl_place_out& q = ctx->dq;
     CU(dalloc(&q.md5, 16 * n)); CU(dalloc(&q.hash, n)); CU(dalloc(&q.node, n));
     CU(dalloc(&ctx->d_ch_len, n)); CU(dalloc(&ctx->d_ch_size, n)); CU(dalloc(&ctx->d_ch_ok, n));
-    CU(cudaFuncSetAttribute(shl::k_route<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
-    CU(cudaFuncSetAttribute(shl::k_route<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
+    CU(cudaFuncSetAttribute(shl::k_route<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
+    CU(cudaFuncSetAttribute(shl::k_route<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
+    CU(cudaFuncSetAttribute(shl::k_route<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
+    CU(cudaFuncSetAttribute(shl::k_route<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
     for (auto& st : ctx->pipe) CU(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
     for (auto& e : ctx->ev_join) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -388,9 +390,11 @@ static int launch_route(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_
         a.ring_values = ctx->d_ring_values; a.ring_nodes = ctx->d_ring_nodes; a.ring_dir = ctx->d_ring_dir;
         a.n_points = ctx->n_points; a.n_hosts = ctx->n_hosts; a.place = *d_q;
         const size_t sh = (d_q->hist && ctx->n_hosts <= 4096u) ? ctx->n_hosts * 4 : 0;
-        shl::k_route<true><<<blocks, shl::kWarpsPerBlock * 32, sh, stream>>>(a);
+        if (gsz == shl::kGroup) shl::k_route<true, true><<<blocks, shl::kWarpsPerBlock * 32, sh, stream>>>(a);
+        else shl::k_route<true, false><<<blocks, shl::kWarpsPerBlock * 32, sh, stream>>>(a);
     } else {
-        shl::k_route<false><<<blocks, shl::kWarpsPerBlock * 32, 0, stream>>>(a);
+        if (gsz == shl::kGroup) shl::k_route<false, true><<<blocks, shl::kWarpsPerBlock * 32, 0, stream>>>(a);
+        else shl::k_route<false, false><<<blocks, shl::kWarpsPerBlock * 32, 0, stream>>>(a);
     }
     ctx->launches++;
     CU(cudaGetLastError());

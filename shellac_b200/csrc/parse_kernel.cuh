@@ -532,7 +532,7 @@ __device__ __noinline__ int find_term_scalar(const uint8_t* m, int from, int L) 
 }
 
 // ----------------------------------------------------------------------------------- kernel
-template <bool kPlace>
+template <bool kPlace, bool kFull>     // kFull: 32 messages per warp (compile-time), else a.group of them
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_route(const RouteArgs a) {
     __shared__ uint16_t s_cr[kWarpsPerBlock][kCrCap * 32 + 2];       // + a spare slot for branch-free writes
     __shared__ uint16_t s_sp[kWarpsPerBlock][kSepCap * 32 + 2];
@@ -549,8 +549,9 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
     // (A block-level counting sort of the messages by scan length, so that the lanes of a warp
     // finish together, was tried here: 1.6 % faster and one more thing to get wrong.  Not kept.)
     {
-        const uint64_t mine = ((uint64_t)blockIdx.x * kWarpsPerBlock + warp) * a.group + lane;
-        const bool have = (uint32_t)lane < a.group && mine < a.n;
+        const uint32_t gsz = kFull ? (uint32_t)kGroup : a.group;
+        const uint64_t mine = ((uint64_t)blockIdx.x * kWarpsPerBlock + warp) * gsz + lane;
+        const bool have = (kFull || (uint32_t)lane < gsz) && mine < a.n;
         const uint64_t my_off = have ? a.off[mine] : 0ull;
         const int L = have ? (int)min(a.len[mine], 0x7fffffc0u) : 0;
         const uint8_t* m = a.arena + my_off;
