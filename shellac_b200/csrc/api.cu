@@ -36,6 +36,7 @@ struct shl_ctx {
     uint64_t* d_koff = nullptr; uint32_t* d_klen = nullptr;
     shl_parse_out dp{}; shl_frame_out df{}; shl_place_out dq{};
     shl_parse_out cur_dp{};               // where the LAST *_batch parse left its per-message fields (dp, or the small-batch block)
+    const uint32_t* cur_node = nullptr; const uint64_t* cur_hist = nullptr;   // ... and the last placement its nodes / histogram
     uint64_t* d_counters = nullptr;       // [0]=hdr_used [1]=chunk_used [2..66)=code_hist
     uint64_t* h_counters = nullptr;       // pinned mirror
     int32_t* d_ch_len = nullptr; uint64_t* d_ch_size = nullptr; uint8_t* d_ch_ok = nullptr;
@@ -57,7 +58,7 @@ struct shl_ctx {
     int pipeline = 1;                     // SHL_PIPELINE=0 disables the chunked path
     // small-batch path (one reactor tick): every result of a call lands in ONE device block that
     // comes back with ONE copy into a pinned mirror, and is handed out from there on the host
-    static constexpr uint64_t kSmallMsgs = 8192;
+    static constexpr uint64_t kSmallMsgs = 4096;             // beyond this the host-side hand-out costs more than the copies it saves
     uint8_t* d_small = nullptr; uint8_t* h_small = nullptr; uint64_t small_bytes = 0;
     int small_path = 1;                   // SHL_SMALL=0 disables it
     std::string err;
@@ -515,7 +516,7 @@ static int route_small(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes,
     const uint32_t nh = qout ? ctx->n_hosts : 0u;
     const SmallLayout l = small_layout(n, nh);
     if (!ctx->d_small) {
-        const SmallLayout big = small_layout(shl_ctx::kSmallMsgs, 65536);
+        const SmallLayout big = small_layout(std::min<uint64_t>(shl_ctx::kSmallMsgs, ctx->max_msgs), 4096);   // rings beyond 4 096 hosts take the general path
         CU(cudaMalloc(reinterpret_cast<void**>(&ctx->d_small), big.total));
         CU(cudaHostAlloc(reinterpret_cast<void**>(&ctx->h_small), big.total, cudaHostAllocDefault));
         ctx->small_bytes = big.total;
@@ -538,6 +539,7 @@ static int route_small(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes,
         q.hist = qout->hist ? reinterpret_cast<uint64_t*>(d + l.hist) : nullptr;
     }
     ctx->cur_dp = o;
+    if (qout) { ctx->cur_node = q.node; ctx->cur_hist = q.hist; }
     if (int rc = launch_route(ctx, ctx->d_arena, ctx->d_off, ctx->d_len, n, &o, qout ? &q : nullptr)) return rc;
     CU(cudaMemcpyAsync(ctx->h_small, d, l.total, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
@@ -577,6 +579,7 @@ static int route_pipelined(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_by
     constexpr int kPipe = shl_ctx::kPipe, kMaxChunks = shl_ctx::kMaxChunks;
     if (!ctx->pipeline || !arena || n < 65536) return 1;
     ctx->cur_dp = ctx->dp;
+    if (qout) { ctx->cur_node = ctx->dq.node; ctx->cur_hist = ctx->d_hist; }
     const int nch = (int)std::min<uint64_t>(kMaxChunks, std::max<uint64_t>(2, n / 65536));
     const uint64_t per = ((n + nch - 1) / nch + 31) & ~31ull;
     // cheap density probe (the exact byte range of a chunk is computed right before it is queued,
@@ -686,6 +689,7 @@ int shl_route_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, co
     dq.hist = qout->hist ? ctx->d_hist : nullptr;
     if (dq.hist) CU(cudaMemsetAsync(ctx->d_hist, 0, (size_t)ctx->n_hosts * 8, ctx->stream));
     ctx->cur_dp = ctx->dp;
+    ctx->cur_node = ctx->dq.node; ctx->cur_hist = ctx->d_hist;
     if (int rc = shl_route_dev(ctx, ctx->d_arena, ctx->d_off, ctx->d_len, n, &ctx->dp, &dq)) return rc;
     if (int rc = parse_out_d2h(ctx, pout, n)) return rc;
     return place_out_d2h(ctx, qout, n);
@@ -699,6 +703,7 @@ int shl_place_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, co
     shl_place_out dq = ctx->dq;
     dq.hist = out->hist ? ctx->d_hist : nullptr;
     if (dq.hist) CU(cudaMemsetAsync(ctx->d_hist, 0, (size_t)ctx->n_hosts * 8, ctx->stream));
+    ctx->cur_node = ctx->dq.node; ctx->cur_hist = ctx->d_hist;
     if (int rc = shl_place_dev(ctx, ctx->d_arena, ctx->d_koff, ctx->d_klen, n, &dq)) return rc;
     return place_out_d2h(ctx, out, n);
 }
@@ -795,7 +800,8 @@ int shl_group_batch(shl_ctx* ctx, uint64_t n, uint32_t* start, uint32_t* order) 
         CU(dalloc(&ctx->d_gstart, ctx->n_hosts + 1)); CU(dalloc(&ctx->d_gcursor, ctx->n_hosts + 1));
         ctx->gcap = ctx->n_hosts + 1;
     }
-    if (int rc = shl_group_dev(ctx, ctx->dq.node, n, ctx->n_hosts, ctx->d_hist, ctx->d_gstart, ctx->d_gcursor, ctx->d_gorder)) return rc;
+    if (!ctx->cur_node || !ctx->cur_hist) return fail(ctx, SHL_ERR_ARG, "shl_group_batch needs a preceding route / place call with a histogram");
+    if (int rc = shl_group_dev(ctx, ctx->cur_node, n, ctx->n_hosts, ctx->cur_hist, ctx->d_gstart, ctx->d_gcursor, ctx->d_gorder)) return rc;
     CU(cudaMemcpyAsync(start, ctx->d_gstart, (size_t)(ctx->n_hosts + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaMemcpyAsync(order, ctx->d_gorder, n * 4, cudaMemcpyDeviceToHost, ctx->stream));   // only start[n_hosts] entries are meaningful
     return SHL_OK;

@@ -183,7 +183,7 @@ def test_fresh_engines_give_the_same_records_every_time(golden):
 
 
 def test_host_paths_small_block_and_field_by_field_agree(golden, monkeypatch):
-    """Batches of up to 8 192 messages come back through one device block and one copy
+    """Batches of up to 4 096 messages come back through one device block and one copy
     (route_small in api.cu); SHL_SMALL=0 forces the field-by-field path the larger ones take.
     Both against the oracle, including frame + body gather continuing from either."""
     from shellac_b200.engine import Engine
@@ -204,6 +204,13 @@ def test_host_paths_small_block_and_field_by_field_agree(golden, monkeypatch):
             assert_frame_equal(ar, fo, of, 'frame after SHL_SMALL=' + small)
             bo, ob = e.body(ar), O.orc_body(ar, o, of)
             assert (bo.body_len[:ar.n] == ob.body_len[:ar.n]).all()
+            start, order = e.group(ar.n)                      # must see THIS call's nodes, wherever they live on the device
+            node = qo.node[:ar.n]
+            placed = node != 0xffffffff
+            assert int(start[len(hosts)]) == int(placed.sum())
+            assert (np.diff(start.astype(np.int64)) == np.bincount(node[placed], minlength=len(hosts))).all()
+            got = order[:int(start[len(hosts)])]
+            assert (node[got] == np.repeat(np.arange(len(hosts)), np.diff(start.astype(np.int64)))).all()
             outs.append((qo.node[:ar.n].copy(), qo.hash[:ar.n].copy(), qo.hist.copy()))
         finally:
             e.close()
