@@ -43,3 +43,17 @@ for _ in range(300):
     eng.lib.shl_route_batch(*args)
     ts.append(time.perf_counter() - t0)
 print('n=%d bare C ABI call: median %.1f us' % (n, np.median(np.array(ts) * 1e6)))
+
+# the reactor shim's router (what one epoll tick pays end to end, packing included)
+from shellac_b200.reactor import EngineRouter
+router = EngineRouter(eng)
+for n in (1, 64, 512):
+    msgs = [ar.message(i % ar.n) for i in range(n)]
+    for _ in range(5):
+        router.route(msgs)
+    ts = []
+    for _ in range(50):
+        t0 = time.perf_counter()
+        router.route(msgs)
+        ts.append(time.perf_counter() - t0)
+    print('EngineRouter.route n=%d: median %.1f us' % (n, np.median(np.array(ts) * 1e6)))
