@@ -9,7 +9,7 @@ import ctypes as C
 import numpy as np
 
 from . import _native as N
-from .batch import Arena, BodyOut, FrameOut, ParseOut, PlaceOut
+from .batch import Arena, BodyOut, FrameOut, ParseOut, PlaceOut  # noqa: F401
 
 
 def _check(lib, ctx, rc, what):
@@ -176,9 +176,9 @@ class Engine(object):
         self.sync()
         return start, order[:n]
 
-    def chunk_header(self, arena):
+    def chunk_header(self, arena, out=None):
         n = arena.n
-        hl, sz, ok = self.pinned(n, np.int32), self.pinned(n, np.uint64), self.pinned(n, np.uint8)
+        hl, sz, ok = out if out is not None else (self.pinned(n, np.int32), self.pinned(n, np.uint64), self.pinned(n, np.uint8))
         rc = self.lib.shl_chunk_header_batch(self.ctx, arena.data.ctypes.data, arena.nbytes, arena.off.ctypes.data,
                                              arena.len.ctypes.data, n, hl.ctypes.data, sz.ctypes.data, ok.ctypes.data)
         _check(self.lib, self.ctx, rc, 'shl_chunk_header_batch')
@@ -244,6 +244,52 @@ class Engine(object):
             self.close()
         except Exception:   # noqa: BLE001 - interpreter shutdown
             pass
+
+
+class PinnedBatch(object):
+    """A pinned arena plus result arrays that live between calls and only grow.  Page-locking
+    memory costs more than parsing a reactor tick's worth of requests, so the callers that run
+    many small batches (the reactor shim, the incremental HttpParser facade) pack into this."""
+
+    def __init__(self, eng, msgs=64, nbytes=1 << 16):
+        self.eng = eng
+        self._cap_n = self._cap_b = 0
+        self._hosts = -1
+        self._fout = None
+        self.grow(msgs, nbytes)
+
+    def grow(self, n, nbytes):
+        eng = self.eng
+        if n > self._cap_n or nbytes > self._cap_b:
+            n, nbytes = max(n, 2 * self._cap_n, 64), max(nbytes, 2 * self._cap_b, 1 << 16)
+            self.data = eng.pinned(nbytes + 64, np.uint8)
+            self.off, self.len = eng.pinned(n, np.uint64), eng.pinned(n, np.uint32)
+            self.pout = ParseOut(n, 24 * n + 64, alloc=eng.pinned)
+            self._cap_n, self._cap_b, self._hosts, self._fout = n, nbytes, -1, None
+        if eng.n_hosts != self._hosts:
+            self.qout = PlaceOut(self._cap_n, max(eng.n_hosts, 1), alloc=eng.pinned)
+            self._hosts = eng.n_hosts
+
+    @property
+    def fout(self):
+        if self._fout is None:
+            self._fout = FrameOut(self._cap_n, self._cap_b // 5 + 64, alloc=self.eng.pinned)
+        return self._fout
+
+    def pack(self, messages):
+        msgs = [m.encode('latin-1') if isinstance(m, str) else bytes(m) for m in messages]
+        n = len(msgs)
+        lens = np.fromiter((len(m) for m in msgs), dtype=np.uint32, count=n)
+        total = int(lens.sum())
+        self.grow(n, total)
+        self.data[:total] = np.frombuffer(b''.join(msgs), dtype=np.uint8)
+        self.data[total:total + 64] = 0
+        if n:
+            self.len[:n] = lens
+            self.off[0] = 0
+        if n > 1:
+            np.cumsum(lens[:-1], dtype=np.uint64, out=self.off[1:n])
+        return Arena(self.data, self.off[:n], self.len[:n])
 
 
 class DeviceBatch(object):

@@ -14,10 +14,8 @@ peeled off in further rounds of the same tick (Server.py:320 `while len(data) !=
 `router` is anything with `route(messages) -> (parse_out, place_out, frame_out_or_None)`;
 `EngineRouter` below is the real one.  There is no CPU path in this package.
 """
-import numpy as np
-
 from . import _native as N
-from .batch import Arena, MessageView, ParseOut, PlaceOut
+from .batch import MessageView
 
 
 class Routed(object):
@@ -36,33 +34,9 @@ class EngineRouter(object):
     bytes into the arena, one C call, and copies of the rows that were filled."""
 
     def __init__(self, engine, msgs=256, nbytes=1 << 18):
+        from .engine import PinnedBatch
         self.eng = engine
-        self._cap_n = self._cap_b = 0
-        self._hosts = -1
-        self._grow(msgs, nbytes)
-
-    def _grow(self, n, nbytes):
-        eng = self.eng
-        if n > self._cap_n or nbytes > self._cap_b or eng.n_hosts != self._hosts:
-            n, nbytes = max(n, 2 * self._cap_n, 64), max(nbytes, 2 * self._cap_b, 1 << 16)
-            self._data = eng.pinned(nbytes + 64, np.uint8)
-            self._off, self._len = eng.pinned(n, np.uint64), eng.pinned(n, np.uint32)
-            self._pout = ParseOut(n, 24 * n + 64, alloc=eng.pinned)
-            self._qout = PlaceOut(n, max(eng.n_hosts, 1), alloc=eng.pinned)
-            self._cap_n, self._cap_b, self._hosts = n, nbytes, eng.n_hosts
-
-    def _pack(self, messages):
-        msgs = [m.encode('latin-1') if isinstance(m, str) else m for m in messages]
-        n = len(msgs)
-        lens = np.fromiter((len(m) for m in msgs), dtype=np.uint32, count=n)
-        total = int(lens.sum())
-        self._grow(n, total)
-        self._data[:total] = np.frombuffer(b''.join(msgs), dtype=np.uint8)
-        self._len[:n] = lens
-        self._off[0] = 0
-        if n > 1:
-            np.cumsum(lens[:-1], dtype=np.uint64, out=self._off[1:n])
-        return Arena(self._data, self._off[:n], self._len[:n])
+        self._pb = PinnedBatch(engine, msgs, nbytes)
 
     def route(self, messages):
         eng = self.eng
@@ -70,21 +44,18 @@ class EngineRouter(object):
             ar = eng.pack(messages)
             pout, qout = eng.route(ar)
             return _detach_parse(pout, 0), _detach_place(qout, 0), None
-        ar = self._pack(messages)
-        pout, qout = eng.route(ar, pout=self._pout, qout=self._qout)
+        pb = self._pb
+        ar = pb.pack(messages)
+        pout, qout = eng.route(ar, pout=pb.pout, qout=pb.qout)
         fout = None
         if ((pout.status[:ar.n] & N.F_CHUNKED) != 0).any():
-            mark = len(eng._pinned)
-            try:
-                fout = _detach_frame(eng.frame(ar, pout, reuse_arena=True), ar.n)
-            finally:
-                eng.release_pinned(mark)
+            fout = _detach_frame(eng.frame(ar, pout, reuse_arena=True, out=pb.fout, chunk_cap=pb.fout.chunk_cap), ar.n)
         return _detach_parse(pout, ar.n), _detach_place(qout, ar.n), fout
 
     def place_keys(self, keys):
         eng = self.eng
-        ar = self._pack(keys)
-        out = eng.place(ar, out=self._qout)
+        ar = self._pb.pack(keys)
+        out = eng.place(ar, out=self._pb.qout)
         return out.node[:len(keys)].copy()
 
 
@@ -104,7 +75,7 @@ def _detach_frame(f, n):
     b = _Bag()
     for name, _ in N.FRAME_FIELDS:
         setattr(b, name, getattr(f, name)[:n].copy())
-    b.chunk = f.chunk.copy()
+    b.chunk = f.chunk[:int(f.chunk_used[0])].copy()
     return b
 
 

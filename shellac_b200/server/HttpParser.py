@@ -20,6 +20,8 @@ Type rule: feed `str` and the getters return `str` (latin-1), feed `bytes` and t
 import io
 import zlib
 
+import numpy as np
+
 from .. import _native as N
 from ..batch import MessageView
 
@@ -34,29 +36,23 @@ class DeviceBackend(object):
             from ..engine import Engine
             engine = Engine(device=0, max_msgs=1 << 12, max_bytes=1 << 26)
         self.eng = engine
+        from ..engine import PinnedBatch
+        self._pb = PinnedBatch(engine)
+        self._ch = (engine.pinned(1, np.int32), engine.pinned(1, np.uint64), engine.pinned(1, np.uint8))
 
     def views(self, bufs, frame=False):
-        """MessageView per buffer (bytes).  The views own copies, the pinned scratch is released."""
-        eng = self.eng
-        mark = len(eng._pinned)
-        try:
-            ar = eng.pack(bufs)
-            po = eng.parse(ar)
-            fo = eng.frame(ar, po, reuse_arena=True) if frame else None
-            out = [MessageView(bufs[i], _Row(po, i), 0, _FrameRow(fo, i) if fo is not None else None)
-                   for i in range(len(bufs))]
-        finally:
-            eng.release_pinned(mark)
-        return out
+        """MessageView per buffer (bytes).  The views own copies of their rows; the pinned staging
+        area is kept between calls and only grows."""
+        eng, pb = self.eng, self._pb
+        ar = pb.pack(bufs)
+        po = eng.parse(ar, out=pb.pout)
+        fo = eng.frame(ar, po, reuse_arena=True, out=pb.fout, chunk_cap=pb.fout.chunk_cap) if frame else None
+        return [MessageView(bufs[i], _Row(po, i), 0, _FrameRow(fo, i) if fo is not None else None)
+                for i in range(len(bufs))]
 
     def chunk_header(self, buf):
-        eng = self.eng
-        mark = len(eng._pinned)
-        try:
-            hl, sz, ok = eng.chunk_header(eng.pack([buf]))
-            return int(hl[0]), int(sz[0]), bool(ok[0])
-        finally:
-            eng.release_pinned(mark)
+        hl, sz, ok = self.eng.chunk_header(self._pb.pack([buf]), out=self._ch)
+        return int(hl[0]), int(sz[0]), bool(ok[0])
 
 
 class _Row(object):
