@@ -34,7 +34,7 @@ class DeviceBackend(object):
     def __init__(self, engine=None):
         if engine is None:
             from ..engine import Engine
-            engine = Engine(device=0, max_msgs=1 << 12, max_bytes=1 << 26)
+            engine = Engine(device=0, max_msgs=1 << 16, max_bytes=1 << 26)
         self.eng = engine
         from ..engine import PinnedBatch
         self._pb = PinnedBatch(engine)

@@ -382,6 +382,29 @@ def seeded_wellformed(seed, n):
     return out
 
 
+SOUP = ['\r\n', '\r\n', ': ', ': ', ' ', ':', '\r', '\n', '\t', 'a', 'bc', 'Host', 'GET', 'POST', '/x/y', 'HTTP/1.1',
+        'HTTP/1.0', 'HTTP/2', '200', 'OK', 'Content-Length', 'content-length', '5', '-1', '1e3', 'Transfer-Encoding',
+        'chunked', '\r\n\r\n', '\x00', '\x7f', '\x0b', 'HT', '/', '0', 'A: b\r\n']
+
+
+def token_soup(seed, n):
+    """Random sequences of the tokens the grammar is made of, and well-formed skeletons with soup
+    in the values: CRLFs, ': ', spaces and their halves in every neighbourhood (the cases a
+    scanner that works on byte PAIRS across message and vector boundaries has to get right)."""
+    rng = random.Random(seed)
+    out = []
+    while len(out) < n:
+        k = rng.randrange(0, 40)
+        m = ''.join(rng.choice(SOUP) for _ in range(k))
+        if len(out) % 3 == 0:
+            hdrs = ''.join('K%d: %s\r\n' % (h, ''.join(rng.choice(SOUP[2:]) for _ in range(rng.randrange(0, 4))).replace('\r\n', '_'))
+                           for h in range(rng.randrange(0, 12)))
+            m = 'GET /' + m.replace(' ', '').replace('\r', '').replace('\n', '')[:40] + ' HTTP/1.1\r\n' + hdrs + '\r\n'
+        if in_fence(m):
+            out.append(m)
+    return out
+
+
 def handmade():
     """Edge cases named in SURVEY.md section 8(a) (exception taxonomy) and probed quirks."""
     H = 'HTTP/1.1 200 OK\r\n'
@@ -544,6 +567,8 @@ def main():
         g['whole'].append({'id': 'chnk%04d' % i, 'msg': msg, 'obs': drive_whole(msg)})
     for i, msg in enumerate(seeded_wellformed(20130728, 600)):
         g['whole'].append({'id': 'well%04d' % i, 'msg': msg, 'obs': drive_whole(msg)})
+    for i, msg in enumerate(token_soup(20130729, 3000)):
+        g['whole'].append({'id': 'soup%04d' % i, 'msg': msg, 'obs': drive_whole(msg)})
     for name, frags in fragment_fixtures().items():
         g['fragments'].append({'id': name, 'frags': frags, 'obs': drive_fragments(frags)})
     for i, frags in enumerate(random_fragmentations(20130726, 400)):

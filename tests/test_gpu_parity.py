@@ -187,7 +187,7 @@ def test_host_paths_small_block_and_field_by_field_agree(golden, monkeypatch):
     (route_small in api.cu); SHL_SMALL=0 forces the field-by-field path the larger ones take.
     Both against the oracle, including frame + body gather continuing from either."""
     from shellac_b200.engine import Engine
-    msgs = [w['msg'] for w in golden['whole']]
+    msgs = [w['msg'] for w in golden['whole'][::2]][:4000]        # at most 4 096: the one-block path qualifies
     hosts = ['10.0.0.%d' % (i + 1) for i in range(16)]
     outs = []
     for small in ('1', '0'):
