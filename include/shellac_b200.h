@@ -282,8 +282,42 @@ uint64_t shl_launch_count(shl_ctx* ctx);
  * them); the *_dev getters expose the device buffers so a collective can read them in place.    */
 #define SHL_N_CODES 64
 int   shl_code_hist(shl_ctx* ctx, uint64_t* out, int reset);
-void* shl_code_hist_dev(shl_ctx* ctx);   /* uint64_t[SHL_N_CODES]                                  */
+void* shl_code_hist_dev(shl_ctx* ctx);   /* uint64_t[SHL_N_CODES] = shl_stats_dev + n_hosts (moves with it) */
 void* shl_node_hist_dev(shl_ctx* ctx);   /* uint64_t[n_hosts], filled by *_batch calls with hist   */
+/* ------------------------------------------------------------------------------------------
+ * Counters across GPUs.  The path shards by request batch, one process per GPU, with no exchange
+ * of payloads; the ranks of a job only sum their COUNTERS: uint64[n_hosts + SHL_N_CODES], the
+ * per-node placement histogram followed by the per-outcome counts (there is
+ * no counterpart in the reference, which is one single-threaded process).  The library owns two
+ * such device buffers, the NCCL communicator and a side stream.
+ *   shl_stats_dev      the CURRENT buffer: hand it to a *_dev call as place.hist so the kernel adds
+ *                      its histogram there; the outcome counts of every parse/route call land
+ *                      behind it (shl_code_hist_dev points at them).  Changes with every
+ *                      shl_stats_allreduce: ask again after each.
+ *   shl_comm_unique_id / shl_comm_init   rank 0 makes the 128-byte id, ships it to the others by
+ *                      any means (a file, a socket), every rank calls init (collective, blocks).
+ *                      Without a communicator everything below still works, on one rank's counters.
+ *   shl_stats_allreduce  closes the current buffer: summed over the ranks (ncclAllReduce, uint64,
+ *                      sum) on the side stream, ordered after everything queued on the ctx stream,
+ *                      result also copied to pinned host memory; the other buffer, zeroed, becomes
+ *                      current.  Returns at once: the kernel of the next batch overlaps the reduce.
+ *   shl_stats_join     makes the ctx STREAM wait for the outstanding reduces (call it before
+ *                      recording the event that ends a timed region).
+ *   shl_stats_fetch    host side: waits for the most recent reduce, copies out[0:n].
+ *   shl_comm_allreduce_u64  small blocking all-reduce of n <= 64 host values (op 0 = sum, 1 = max)
+ *                      after draining this ctx's streams: a barrier, the max of a timing over ranks.
+ * ---------------------------------------------------------------------------------------- */
+#define SHL_COMM_ID_BYTES 128
+void*    shl_stats_dev(shl_ctx* ctx);
+uint32_t shl_stats_len(shl_ctx* ctx);                       /* n_hosts + SHL_N_CODES */
+int   shl_comm_unique_id(uint8_t* id, uint32_t cap);        /* cap >= SHL_COMM_ID_BYTES */
+int   shl_comm_init(shl_ctx* ctx, const uint8_t* id, int rank, int world);
+int   shl_comm_size(shl_ctx* ctx);
+int   shl_stats_allreduce(shl_ctx* ctx);
+int   shl_stats_join(shl_ctx* ctx);
+int   shl_stats_fetch(shl_ctx* ctx, uint64_t* out, uint32_t n);
+int   shl_comm_allreduce_u64(shl_ctx* ctx, uint64_t* vals, uint32_t n, int op);
+
 /* Test hook: route every message through the scalar (non-vectorised) device path. */
 int   shl_set_force_scalar(shl_ctx* ctx, int on);
 

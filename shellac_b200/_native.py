@@ -27,6 +27,7 @@ F_STATUS_WIDE, F_CLEN_WIDE, F_FIRST_LINE_DONE = 1 << 15, 1 << 16, 1 << 17
 FS_NOT_CHUNKED = 0xff
 RING_KETAMA, RING_KETAMA_WEIGHTED = 0, 1
 N_CODES = 64          # SHL_N_CODES: histogram length for per-outcome counts
+COMM_ID_BYTES = 128   # SHL_COMM_ID_BYTES
 
 CODE_NAMES = {
     0: 'OK', 1: 'EMPTY', 2: 'INCOMPLETE_LINE', 3: 'INCOMPLETE_HEADERS', 4: 'INCOMPLETE_BODY',
@@ -135,6 +136,15 @@ def lib():
         'shl_code_hist_dev': (vp, [vp]),
         'shl_node_hist_dev': (vp, [vp]),
         'shl_set_force_scalar': (i32, [vp, i32]),
+        'shl_stats_dev': (vp, [vp]),
+        'shl_stats_len': (C.c_uint32, [vp]),
+        'shl_comm_unique_id': (i32, [vp, C.c_uint32]),
+        'shl_comm_init': (i32, [vp, vp, i32, i32]),
+        'shl_comm_size': (i32, [vp]),
+        'shl_stats_allreduce': (i32, [vp]),
+        'shl_stats_join': (i32, [vp]),
+        'shl_stats_fetch': (i32, [vp, vp, C.c_uint32]),
+        'shl_comm_allreduce_u64': (i32, [vp, vp, C.c_uint32, i32]),
         'shl_corpus_lengths_host': (i32, [u64, u64, u64, i32, vp]),
         'shl_corpus_fill_host': (i32, [u64, u64, u64, i32, vp, vp]),
         'shl_corpus_lengths_dev': (i32, [vp, u64, u64, u64, i32, vp]),

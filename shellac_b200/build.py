@@ -13,10 +13,10 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 OUT = os.path.join(HERE, 'libshellac_b200.so')
 SOURCES = ['api.cu']
-DEPS = ['api.cu', 'parse_kernel.cuh', 'frame_kernel.cuh', 'shl_device.cuh', 'corpus.cuh',
+DEPS = ['api.cu', 'parse_kernel.cuh', 'bitmap_walk.cuh', 'frame_kernel.cuh', 'shl_device.cuh', 'corpus.cuh',
         os.path.join('..', '..', 'include', 'shellac_b200.h')]
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17',
-              '-Xcompiler', '-fPIC', '-shared', '-cudart', 'static']
+              '-Xcompiler', '-fPIC', '-shared', '-cudart', 'static', '-ldl']
 
 
 def stale():

@@ -12,6 +12,9 @@
 #include <string>
 #include <vector>
 
+#include <dlfcn.h>
+#include <nccl.h>      // types and prototypes only: the library is bound at run time (see NcclApi)
+
 #include "parse_kernel.cuh"
 #include "frame_kernel.cuh"
 #include "corpus.cuh"
@@ -47,7 +50,17 @@ struct shl_ctx {
     uint64_t* d_hist = nullptr; uint32_t hist_cap = 0;
     uint32_t* d_gstart = nullptr; uint32_t* d_gcursor = nullptr; uint32_t* d_gorder = nullptr; uint32_t gcap = 0;   // grouping (lazy)
     uint8_t* d_body = nullptr; uint64_t* d_body_off = nullptr; uint64_t* d_body_len = nullptr;   // body gather (lazy)
+    // counters shared between GPUs: [placement histogram n_hosts | outcome codes 64], two buffers so
+    // that the all-reduce of batch k (comm stream) overlaps the kernel of batch k + 1 (ctx stream)
+    uint64_t* d_stats[2] = {nullptr, nullptr}; uint64_t* h_stats = nullptr;   // h_stats: pinned, 2 x stats_len
+    uint32_t stats_len = 0; int stat_k = 0, stat_last = -1;
+    cudaStream_t comm_stream = nullptr;
+    cudaEvent_t ev_stats_ready[2]{}, ev_stats_done[2]{};
+    ncclComm_t comm = nullptr; int comm_rank = 0, comm_world = 1;
+    uint64_t* d_scratch = nullptr; uint64_t* h_scratch = nullptr;             // 64 words for shl_comm_allreduce_u64
+    uint64_t cur_n = 0;                   // messages of the last *_batch parse (frame_batch checks it)
     int force_scalar = 0;
+    int sm_count = 148, grid_waves = 16;
     uint64_t launches = 0;
     // pipelined host-buffer path: chunks round-robin over these streams so H2D, kernel and D2H overlap
     static constexpr int kPipe = 4, kMaxChunks = 16;
@@ -77,6 +90,43 @@ int fail(shl_ctx* c, int code, const std::string& msg) {
         if (e_ != cudaSuccess)                                                                \
             return fail(ctx, SHL_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
     } while (0)
+
+// NCCL is bound with dlopen when the first communicator is made, not with a DT_NEEDED entry: a
+// process that loads this library and then imports PyTorch would otherwise be handed the system's
+// libnccl.so.2 where torch expects the newer one it bundles under the same soname (and fails with
+// an undefined symbol).  If NCCL is already in the process (torch's), dlopen returns that copy.
+struct NcclApi {
+    decltype(&ncclGetUniqueId) GetUniqueId = nullptr;
+    decltype(&ncclCommInitRank) CommInitRank = nullptr;
+    decltype(&ncclAllReduce) AllReduce = nullptr;
+    decltype(&ncclCommDestroy) CommDestroy = nullptr;
+    decltype(&ncclGetErrorString) GetErrorString = nullptr;
+    void* handle = nullptr;
+    std::string why;
+    bool load() {
+        if (handle) return true;
+        const char* name = getenv("SHL_NCCL_LIB");
+        handle = dlopen(name && name[0] ? name : "libnccl.so.2", RTLD_NOW | RTLD_LOCAL);
+        if (!handle) { why = std::string("dlopen(libnccl.so.2): ") + dlerror(); return false; }
+#define SHL_NCCL_SYM(f) f = reinterpret_cast<decltype(f)>(dlsym(handle, "nccl" #f)); if (!f) { why = "libnccl.so.2 lacks nccl" #f; handle = nullptr; return false; }
+        SHL_NCCL_SYM(GetUniqueId) SHL_NCCL_SYM(CommInitRank) SHL_NCCL_SYM(AllReduce) SHL_NCCL_SYM(CommDestroy) SHL_NCCL_SYM(GetErrorString)
+#undef SHL_NCCL_SYM
+        return true;
+    }
+};
+NcclApi g_nccl;
+
+// Makes `device` current for the scope and puts the caller's device back on the way out.
+struct DeviceGuard {
+    int prev = -1; bool switched = false;
+    cudaError_t enter(int device) {
+        cudaError_t e = cudaGetDevice(&prev);
+        if (e != cudaSuccess) return e;
+        if (prev != device) { e = cudaSetDevice(device); switched = e == cudaSuccess; }
+        return e;
+    }
+    ~DeviceGuard() { if (switched) cudaSetDevice(prev); }
+};
 
 template <typename T>
 cudaError_t dalloc(T** p, uint64_t n) { return cudaMalloc(reinterpret_cast<void**>(p), std::max<uint64_t>(n, 1) * sizeof(T)); }
@@ -141,6 +191,8 @@ uint64_t parse_block_bytes(uint64_t n) { return 10 * ((n * 4 + 15) & ~15ull) + (
 
 extern "C" {
 
+void shl_ctx_destroy(shl_ctx* ctx);
+
 int shl_device_count(void) {
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
@@ -154,20 +206,23 @@ int shl_device_pci_bus_id(int device, char* buf, int len) {
 
 const char* shl_last_error(shl_ctx* ctx) { return ctx ? ctx->err.c_str() : g_last_error.c_str(); }
 
-int shl_ctx_create(int device, uint64_t max_msgs, uint64_t max_bytes, uint64_t max_records, shl_ctx** out) {
-    shl_ctx* ctx = nullptr;
-    if (!out) return fail(nullptr, SHL_ERR_ARG, "shl_ctx_create: out is null");
-    int ndev = 0;
-    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
-        return fail(nullptr, SHL_ERR_NO_DEVICE, "no CUDA device: libshellac_b200 has no CPU fallback");
-    if (device < 0 || device >= ndev) return fail(nullptr, SHL_ERR_ARG, "shl_ctx_create: bad device index");
-    ctx = new shl_ctx();
-    ctx->device = device;
-    ctx->max_msgs = std::max<uint64_t>(max_msgs, 1);
-    ctx->max_bytes = std::max<uint64_t>(max_bytes, 64);
-    ctx->max_records = max_records ? max_records : std::max<uint64_t>(ctx->max_bytes / 16, 1024);
+static int stats_alloc(shl_ctx* ctx, uint32_t n_hosts) {
+    const uint32_t len = n_hosts + SHL_N_CODES;
+    for (int k = 0; k < 2; k++) { cudaFree(ctx->d_stats[k]); ctx->d_stats[k] = nullptr; }
+    if (ctx->h_stats) { cudaFreeHost(ctx->h_stats); ctx->h_stats = nullptr; }
+    for (int k = 0; k < 2; k++) { CU(dalloc(&ctx->d_stats[k], len)); CU(cudaMemset(ctx->d_stats[k], 0, (size_t)len * 8)); }
+    CU(cudaHostAlloc(reinterpret_cast<void**>(&ctx->h_stats), 2 * (size_t)len * 8, cudaHostAllocDefault));
+    memset(ctx->h_stats, 0, 2 * (size_t)len * 8);
+    ctx->stats_len = len; ctx->stat_k = 0; ctx->stat_last = -1;
+    return SHL_OK;
+}
+static uint64_t* cur_codes(shl_ctx* ctx) { return ctx->d_stats[ctx->stat_k] + (ctx->stats_len - SHL_N_CODES); }
+
+static int ctx_setup(shl_ctx* ctx, int device) {
     CU(cudaSetDevice(device));
     CU(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    CU(cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device));
+    { const char* gw = getenv("SHL_GRID_WAVES"); if (gw && atoi(gw) > 0) ctx->grid_waves = atoi(gw); }
     for (auto& e : ctx->ev) CU(cudaEventCreate(&e));
     const uint64_t n = ctx->max_msgs;
     CU(dalloc(&ctx->d_arena, ctx->max_bytes + 64));
@@ -175,6 +230,12 @@ int shl_ctx_create(int device, uint64_t max_msgs, uint64_t max_bytes, uint64_t m
     CU(dalloc(&ctx->d_koff, n)); CU(dalloc(&ctx->d_klen, n));
     CU(dalloc(&ctx->d_counters, 66));
     CU(cudaHostAlloc(reinterpret_cast<void**>(&ctx->h_counters), 66 * sizeof(uint64_t), cudaHostAllocDefault));
+    if (int rc = stats_alloc(ctx, 0)) return rc;
+    CU(cudaStreamCreateWithFlags(&ctx->comm_stream, cudaStreamNonBlocking));
+    for (auto& e : ctx->ev_stats_ready) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (auto& e : ctx->ev_stats_done) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    CU(dalloc(&ctx->d_scratch, 64));
+    CU(cudaHostAlloc(reinterpret_cast<void**>(&ctx->h_scratch), 64 * sizeof(uint64_t), cudaHostAllocDefault));
     void* blk = nullptr;
     CU(cudaMalloc(&blk, parse_block_bytes(n)));
     shl_hdr_span* hdr = nullptr; CU(dalloc(&hdr, ctx->max_records));
@@ -201,32 +262,59 @@ int shl_ctx_create(int device, uint64_t max_msgs, uint64_t max_bytes, uint64_t m
     { const char* sm = getenv("SHL_SMALL"); if (sm && sm[0] == '0') ctx->small_path = 0; }
     const char* fs = getenv("SHL_FORCE_SCALAR");
     ctx->force_scalar = (fs && fs[0] == '1') ? 1 : 0;
+    return SHL_OK;
+}
+
+int shl_ctx_create(int device, uint64_t max_msgs, uint64_t max_bytes, uint64_t max_records, shl_ctx** out) {
+    if (!out) return fail(nullptr, SHL_ERR_ARG, "shl_ctx_create: out is null");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(nullptr, SHL_ERR_NO_DEVICE, "no CUDA device: libshellac_b200 has no CPU fallback");
+    if (device < 0 || device >= ndev) return fail(nullptr, SHL_ERR_ARG, "shl_ctx_create: bad device index");
+    shl_ctx* ctx = new shl_ctx();
+    ctx->device = device;
+    ctx->max_msgs = std::max<uint64_t>(max_msgs, 1);
+    ctx->max_bytes = std::max<uint64_t>(max_bytes, 64);
+    ctx->max_records = max_records ? max_records : std::max<uint64_t>(ctx->max_bytes / 16, 1024);
+    if (const int rc = ctx_setup(ctx, device)) {           // frees whatever was allocated before the failure
+        const std::string why = ctx->err;
+        shl_ctx_destroy(ctx);
+        return fail(nullptr, rc, why);
+    }
     *out = ctx;
     return SHL_OK;
 }
 
 void shl_ctx_destroy(shl_ctx* ctx) {
     if (!ctx) return;
-    cudaSetDevice(ctx->device);
-    cudaStreamSynchronize(ctx->stream);
+    DeviceGuard guard; guard.enter(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     cudaFree(ctx->d_arena); cudaFree(ctx->d_off); cudaFree(ctx->d_len); cudaFree(ctx->d_koff); cudaFree(ctx->d_klen);
     cudaFree(ctx->dp.status); cudaFree(ctx->dp.hdr);
     cudaFree(ctx->df.fstatus); cudaFree(ctx->df.n_chunks); cudaFree(ctx->df.chunk_base); cudaFree(ctx->df.body_end);
     cudaFree(ctx->df.body_bytes); cudaFree(ctx->df.last_call); cudaFree(ctx->df.chunk);
     cudaFree(ctx->dq.md5); cudaFree(ctx->dq.hash); cudaFree(ctx->dq.node);
     cudaFree(ctx->d_ch_len); cudaFree(ctx->d_ch_size); cudaFree(ctx->d_ch_ok);
-    cudaFree(ctx->d_counters); cudaFreeHost(ctx->h_counters);
+    if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
+    cudaFree(ctx->d_counters);
+    if (ctx->comm) g_nccl.CommDestroy(ctx->comm);
+    for (int k = 0; k < 2; k++) cudaFree(ctx->d_stats[k]);
+    if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
+    cudaFree(ctx->d_scratch); if (ctx->h_scratch) cudaFreeHost(ctx->h_scratch);
+    if (ctx->comm_stream) { cudaStreamSynchronize(ctx->comm_stream); cudaStreamDestroy(ctx->comm_stream); }
+    for (auto& e : ctx->ev_stats_ready) if (e) cudaEventDestroy(e);
+    for (auto& e : ctx->ev_stats_done) if (e) cudaEventDestroy(e);
     cudaFree(ctx->d_ring_values); cudaFree(ctx->d_ring_nodes); cudaFree(ctx->d_ring_dir); cudaFree(ctx->d_hist);
     cudaFree(ctx->d_body); cudaFree(ctx->d_body_off); cudaFree(ctx->d_body_len);
     cudaFree(ctx->d_gstart); cudaFree(ctx->d_gcursor); cudaFree(ctx->d_gorder);
-    for (auto& e : ctx->ev) cudaEventDestroy(e);
-    for (auto& st : ctx->pipe) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
-    cudaEventDestroy(ctx->ev_fork);
-    for (auto& e : ctx->ev_join) cudaEventDestroy(e);
-    for (auto& e : ctx->ev_chunk) cudaEventDestroy(e);
-    cudaFree(ctx->d_chunk_used); cudaFreeHost(ctx->h_chunk_used);
+    for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
+    for (auto& st : ctx->pipe) if (st) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
+    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+    for (auto& e : ctx->ev_join) if (e) cudaEventDestroy(e);
+    for (auto& e : ctx->ev_chunk) if (e) cudaEventDestroy(e);
+    cudaFree(ctx->d_chunk_used); if (ctx->h_chunk_used) cudaFreeHost(ctx->h_chunk_used);
     cudaFree(ctx->d_small); if (ctx->h_small) cudaFreeHost(ctx->h_small);
-    cudaStreamDestroy(ctx->stream);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
 
@@ -339,6 +427,10 @@ int shl_ring_build(shl_ctx* ctx, const char* const* hosts, const uint32_t* ports
         if (!ctx->d_ring_dir) CU(dalloc(&ctx->d_ring_dir, nb + 1));
         CU(cudaMemcpy(ctx->d_ring_dir, dir.data(), (nb + 1) * 4, cudaMemcpyHostToDevice));
     }
+    if (ctx->stats_len != n_hosts + SHL_N_CODES) {
+        CU(cudaStreamSynchronize(ctx->comm_stream));
+        if (int rc = stats_alloc(ctx, n_hosts)) return rc;
+    }
     ctx->n_points = (uint32_t)pts.size(); ctx->n_hosts = n_hosts;
     if (ctx->hist_cap < n_hosts) {
         cudaFree(ctx->d_hist); ctx->d_hist = nullptr;
@@ -371,12 +463,13 @@ static int launch_route(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_
                         const shl_parse_out* d_out, const shl_place_out* d_q, cudaStream_t stream = nullptr, uint32_t bias = 0) {
     if (!stream && ctx) stream = ctx->stream;
     if (!ctx || !d_arena || !d_off || !d_len || !d_out) return fail(ctx, SHL_ERR_ARG, "null pointer");
+    CU(cudaSetDevice(ctx->device));
     if (int rc = check_arena(ctx, d_arena)) return rc;
     if (d_q && !ctx->d_ring_values) return fail(ctx, SHL_ERR_NO_RING, "shl_ring_build() has not been called");
     if (n == 0) return SHL_OK;
     shl::RouteArgs a{};
     a.arena = d_arena; a.off = d_off; a.len = d_len; a.n = n; a.out = *d_out;
-    a.code_hist = ctx->d_counters + 2; a.force_scalar = ctx->force_scalar;
+    a.code_hist = cur_codes(ctx); a.force_scalar = ctx->force_scalar;
     a.k = shl::swar_host_consts();
     a.hdr_base_bias = bias;
     // a warp takes 32 messages when there are enough of them to fill the machine; a reactor-sized
@@ -386,7 +479,9 @@ static int launch_route(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_
     while (gsz > 1 && n / gsz < 148ull * 8ull) gsz >>= 1;
     a.group = gsz;
     const uint64_t groups = (n + gsz - 1) / gsz;
-    const unsigned blocks = (unsigned)((groups + shl::kWarpsPerBlock - 1) / shl::kWarpsPerBlock);
+    // no more blocks than the device holds at once (times SHL_GRID_WAVES): each warp then loops over groups
+    const uint64_t resident = (uint64_t)ctx->sm_count * SHL_OPT_MINBLOCKS * (uint64_t)ctx->grid_waves;
+    const unsigned blocks = (unsigned)std::min<uint64_t>((groups + shl::kWarpsPerBlock - 1) / shl::kWarpsPerBlock, resident);
     if (d_q) {
         a.ring_values = ctx->d_ring_values; a.ring_nodes = ctx->d_ring_nodes; a.ring_dir = ctx->d_ring_dir;
         a.n_points = ctx->n_points; a.n_hosts = ctx->n_hosts; a.place = *d_q;
@@ -415,6 +510,7 @@ int shl_frame_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_off, c
                   const uint32_t* d_status, const uint32_t* d_fl, const uint32_t* d_hl, const shl_frame_out* d_out) {
     if (!ctx || !d_arena || !d_off || !d_len || !d_status || !d_fl || !d_hl || !d_out) return fail(ctx, SHL_ERR_ARG, "null pointer");
     if (n == 0) return SHL_OK;
+    CU(cudaSetDevice(ctx->device));
     shl::FrameArgs a{};
     a.arena = d_arena; a.off = d_off; a.len = d_len; a.n = n; a.status = d_status; a.first_line_len = d_fl; a.headers_len = d_hl;
     a.out = *d_out;
@@ -428,6 +524,7 @@ int shl_place_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_key_of
     if (!ctx || !d_arena || !d_key_off || !d_key_len || !d_out) return fail(ctx, SHL_ERR_ARG, "null pointer");
     if (!ctx->d_ring_values) return fail(ctx, SHL_ERR_NO_RING, "shl_ring_build() has not been called");
     if (n == 0) return SHL_OK;
+    CU(cudaSetDevice(ctx->device));
     shl::PlaceArgs a{};
     a.arena = d_arena; a.key_off = d_key_off; a.key_len = d_key_len; a.n = n;
     a.ring_values = ctx->d_ring_values; a.ring_nodes = ctx->d_ring_nodes; a.ring_dir = ctx->d_ring_dir;
@@ -496,7 +593,7 @@ static int place_out_d2h(shl_ctx* ctx, const shl_place_out* out, uint64_t n) {
 struct SmallLayout {
     uint64_t content_len, md5, u32[10], hash, node, used, hist, rec, rec_cap, total;
 };
-static SmallLayout small_layout(uint64_t n, uint32_t n_hosts) {
+static SmallLayout small_layout(uint64_t n, uint32_t n_hosts, uint64_t arena_bytes) {
     SmallLayout l{}; uint64_t o = 0;
     l.md5 = o; o += 16 * n;                                  // 16-byte stores: keep it first (the block is 256-byte aligned)
     l.content_len = o; o += 8 * n;
@@ -506,7 +603,7 @@ static SmallLayout small_layout(uint64_t n, uint32_t n_hosts) {
     o = (o + 7) & ~7ull;
     l.used = o; o += 8;
     l.hist = o; o += 8ull * n_hosts;
-    l.rec = o; l.rec_cap = 24 * n + 64; o += 8 * l.rec_cap;
+    l.rec = o; l.rec_cap = arena_bytes / 5 + 64; o += 8 * l.rec_cap;   // a header line is at least "k: " CRLF: the records always fit
     l.total = o;
     return l;
 }
@@ -514,9 +611,10 @@ static int route_small(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes,
                        uint64_t n, const shl_parse_out* pout, const shl_place_out* qout) {
     if (!ctx->small_path || !arena || n == 0 || n > shl_ctx::kSmallMsgs) return 1;
     const uint32_t nh = qout ? ctx->n_hosts : 0u;
-    const SmallLayout l = small_layout(n, nh);
+    const SmallLayout l = small_layout(n, nh, arena_bytes);
     if (!ctx->d_small) {
-        const SmallLayout big = small_layout(std::min<uint64_t>(shl_ctx::kSmallMsgs, ctx->max_msgs), 4096);   // rings beyond 4 096 hosts take the general path
+        const SmallLayout big = small_layout(std::min<uint64_t>(shl_ctx::kSmallMsgs, ctx->max_msgs), 4096,
+                                             std::min<uint64_t>(ctx->max_bytes, 4ull << 20));   // bigger ticks and rings beyond 4 096 hosts take the general path
         CU(cudaMalloc(reinterpret_cast<void**>(&ctx->d_small), big.total));
         CU(cudaHostAlloc(reinterpret_cast<void**>(&ctx->h_small), big.total, cudaHostAllocDefault));
         ctx->small_bytes = big.total;
@@ -538,14 +636,21 @@ static int route_small(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes,
         q.md5 = d + l.md5; q.hash = reinterpret_cast<uint32_t*>(d + l.hash); q.node = reinterpret_cast<uint32_t*>(d + l.node);
         q.hist = qout->hist ? reinterpret_cast<uint64_t*>(d + l.hist) : nullptr;
     }
-    ctx->cur_dp = o;
+    ctx->cur_dp = o; ctx->cur_n = n;
     if (qout) { ctx->cur_node = q.node; ctx->cur_hist = q.hist; }
     if (int rc = launch_route(ctx, ctx->d_arena, ctx->d_off, ctx->d_len, n, &o, qout ? &q : nullptr)) return rc;
-    CU(cudaMemcpyAsync(ctx->h_small, d, l.total, cudaMemcpyDeviceToHost, ctx->stream));
+    // one copy brings the fields and as many records as a batch normally has (24 per message);
+    // the rare batch with more fetches the rest with a second copy
+    const uint64_t first_recs = std::min<uint64_t>(l.rec_cap, 24 * n + 64);
+    CU(cudaMemcpyAsync(ctx->h_small, d, l.rec + 8 * first_recs, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
     const uint8_t* h = ctx->h_small;
     const uint64_t used = *reinterpret_cast<const uint64_t*>(h + l.used);
-    if (used > l.rec_cap) return 1;                       // more records than the block holds: the general path decides
+    if (used > l.rec_cap) return fail(ctx, SHL_ERR_CAPACITY, "small-batch record block overflowed (cannot happen: a header line is >= 5 bytes)");
+    if (used > first_recs) {
+        CU(cudaMemcpyAsync(ctx->h_small + l.rec + 8 * first_recs, d + l.rec + 8 * first_recs, 8 * (used - first_recs), cudaMemcpyDeviceToHost, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+    }
     if (pout->hdr && used > pout->hdr_cap)
         return fail(ctx, SHL_ERR_CAPACITY, "header record arena overflowed: raise max_records / hdr_cap");
 #define OUT(dst, src_off, bytes) do { if (dst) std::memcpy((dst), h + (src_off), (bytes)); } while (0)
@@ -578,8 +683,8 @@ static int route_pipelined(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_by
                            uint64_t n, const shl_parse_out* pout, const shl_place_out* qout) {
     constexpr int kPipe = shl_ctx::kPipe, kMaxChunks = shl_ctx::kMaxChunks;
     if (!ctx->pipeline || !arena || n < 65536) return 1;
-    ctx->cur_dp = ctx->dp;
-    if (qout) { ctx->cur_node = ctx->dq.node; ctx->cur_hist = ctx->d_hist; }
+    ctx->cur_dp = ctx->dp; ctx->cur_n = n;
+    if (qout) { ctx->cur_node = ctx->dq.node; ctx->cur_hist = qout->hist ? ctx->d_hist : nullptr; }
     const int nch = (int)std::min<uint64_t>(kMaxChunks, std::max<uint64_t>(2, n / 65536));
     const uint64_t per = ((n + nch - 1) / nch + 31) & ~31ull;
     // cheap density probe (the exact byte range of a chunk is computed right before it is queued,
@@ -667,7 +772,7 @@ int shl_parse_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, co
     }
     if (int rc = stage_in(ctx, arena, arena_bytes, off, len, n, ctx->d_off, ctx->d_len)) return rc;
     CU(cudaMemsetAsync(ctx->d_counters, 0, 8, ctx->stream));
-    ctx->cur_dp = ctx->dp;
+    ctx->cur_dp = ctx->dp; ctx->cur_n = n;
     if (int rc = shl_parse_dev(ctx, ctx->d_arena, ctx->d_off, ctx->d_len, n, &ctx->dp)) return rc;
     return parse_out_d2h(ctx, out, n);
 }
@@ -688,8 +793,8 @@ int shl_route_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, co
     shl_place_out dq = ctx->dq;
     dq.hist = qout->hist ? ctx->d_hist : nullptr;
     if (dq.hist) CU(cudaMemsetAsync(ctx->d_hist, 0, (size_t)ctx->n_hosts * 8, ctx->stream));
-    ctx->cur_dp = ctx->dp;
-    ctx->cur_node = ctx->dq.node; ctx->cur_hist = ctx->d_hist;
+    ctx->cur_dp = ctx->dp; ctx->cur_n = n;
+    ctx->cur_node = ctx->dq.node; ctx->cur_hist = dq.hist;
     if (int rc = shl_route_dev(ctx, ctx->d_arena, ctx->d_off, ctx->d_len, n, &ctx->dp, &dq)) return rc;
     if (int rc = parse_out_d2h(ctx, pout, n)) return rc;
     return place_out_d2h(ctx, qout, n);
@@ -703,7 +808,7 @@ int shl_place_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, co
     shl_place_out dq = ctx->dq;
     dq.hist = out->hist ? ctx->d_hist : nullptr;
     if (dq.hist) CU(cudaMemsetAsync(ctx->d_hist, 0, (size_t)ctx->n_hosts * 8, ctx->stream));
-    ctx->cur_node = ctx->dq.node; ctx->cur_hist = ctx->d_hist;
+    ctx->cur_node = ctx->dq.node; ctx->cur_hist = dq.hist;
     if (int rc = shl_place_dev(ctx, ctx->d_arena, ctx->d_koff, ctx->d_klen, n, &dq)) return rc;
     return place_out_d2h(ctx, out, n);
 }
@@ -714,7 +819,7 @@ int shl_frame_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, co
     if (!out || !status || !first_line_len || !headers_len) return fail(ctx, SHL_ERR_ARG, "null pointer");
     if (int rc = stage_in(ctx, arena, arena_bytes, off, len, n, ctx->d_off, ctx->d_len)) return rc;
     // the parse fields travel with the call so it can be used on its own (they are tiny next to the arena)
-    if (n > shl_ctx::kSmallMsgs) ctx->cur_dp = ctx->dp;    // cannot be the continuation of a small-batch parse
+    if (n != ctx->cur_n) { ctx->cur_dp = ctx->dp; ctx->cur_n = n; }   // not the continuation of the last parse: the small-batch block is laid out for ITS n
     const shl_parse_out& cur = ctx->cur_dp;
     CU(cudaMemcpyAsync(cur.status, status, n * 4, cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaMemcpyAsync(cur.first_line_len, first_line_len, n * 4, cudaMemcpyHostToDevice, ctx->stream));
@@ -742,6 +847,7 @@ int shl_body_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_off, co
                  const shl_parse_out* p, const shl_frame_out* f, const shl_body_out* d_out) {
     if (!ctx || !d_arena || !d_off || !d_len || !p || !f || !d_out) return fail(ctx, SHL_ERR_ARG, "null pointer");
     if (n == 0) return SHL_OK;
+    CU(cudaSetDevice(ctx->device));
     shl::BodyArgs a{};
     a.arena = d_arena; a.off = d_off; a.len = d_len; a.n = n;
     a.status = p->status; a.first_line_len = p->first_line_len; a.headers_len = p->headers_len; a.content_len = p->content_len;
@@ -782,6 +888,7 @@ int shl_body_batch(shl_ctx* ctx, uint64_t n, const shl_body_out* out) {
 int shl_group_dev(shl_ctx* ctx, const uint32_t* d_node, uint64_t n, uint32_t n_hosts, const uint64_t* d_hist,
                   uint32_t* d_start, uint32_t* d_cursor, uint32_t* d_order) {
     if (!ctx || !d_node || !d_hist || !d_start || !d_cursor || !d_order || n_hosts == 0) return fail(ctx, SHL_ERR_ARG, "null pointer");
+    CU(cudaSetDevice(ctx->device));
     shl::k_group_scan<<<1, 1024, 0, ctx->stream>>>(d_hist, n_hosts, d_start, d_cursor);
     if (n) shl::k_group_scatter<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(d_node, n, n_hosts, d_cursor, d_order);
     ctx->launches += 2;
@@ -823,15 +930,100 @@ int shl_chunk_header_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_by
 
 int shl_code_hist(shl_ctx* ctx, uint64_t* out64, int reset) {
     if (!ctx || !out64) return SHL_ERR_ARG;
-    CU(cudaMemcpyAsync(ctx->h_counters + 2, ctx->d_counters + 2, 64 * 8, cudaMemcpyDeviceToHost, ctx->stream));
-    if (reset) CU(cudaMemsetAsync(ctx->d_counters + 2, 0, 64 * 8, ctx->stream));
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMemcpyAsync(ctx->h_counters + 2, cur_codes(ctx), 64 * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (reset) CU(cudaMemsetAsync(cur_codes(ctx), 0, 64 * 8, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
     memcpy(out64, ctx->h_counters + 2, 64 * 8);
     return SHL_OK;
 }
-void* shl_code_hist_dev(shl_ctx* ctx) { return ctx ? (void*)(ctx->d_counters + 2) : nullptr; }
+void* shl_code_hist_dev(shl_ctx* ctx) { return ctx ? (void*)cur_codes(ctx) : nullptr; }
 void* shl_node_hist_dev(shl_ctx* ctx) { return ctx ? (void*)ctx->d_hist : nullptr; }
 int shl_set_force_scalar(shl_ctx* ctx, int on) { if (!ctx) return SHL_ERR_ARG; ctx->force_scalar = on ? 1 : 0; return SHL_OK; }
+
+// ------------------------------------------------------------------------------------ counters across GPUs
+// The path has no exchange step: requests are independent and every GPU holds the whole ring.
+// What the ranks of a job share are COUNTERS, `uint64[n_hosts + SHL_N_CODES]` (per-node placement
+// histogram, per-outcome counts).  The library owns them (two device buffers), the NCCL
+// communicator (one rank per process, one process per GPU) and a side stream: the all-reduce of
+// batch k is ordered against the ctx stream by events only, so the kernel of batch k + 1 runs
+// while it is in flight.  No PyTorch anywhere.
+void* shl_stats_dev(shl_ctx* ctx) { return ctx ? (void*)ctx->d_stats[ctx->stat_k] : nullptr; }
+uint32_t shl_stats_len(shl_ctx* ctx) { return ctx ? ctx->stats_len : 0u; }
+
+int shl_comm_unique_id(uint8_t* id, uint32_t cap) {
+    shl_ctx* ctx = nullptr;
+    if (!id || cap < sizeof(ncclUniqueId)) return fail(nullptr, SHL_ERR_ARG, "shl_comm_unique_id: buffer smaller than SHL_COMM_ID_BYTES");
+    if (!g_nccl.load()) return fail(ctx, SHL_ERR_CUDA, g_nccl.why);
+    ncclUniqueId u;
+    const ncclResult_t r = g_nccl.GetUniqueId(&u);
+    if (r != ncclSuccess) return fail(ctx, SHL_ERR_CUDA, std::string("ncclGetUniqueId: ") + g_nccl.GetErrorString(r));
+    memcpy(id, &u, sizeof u);
+    return SHL_OK;
+}
+static_assert(sizeof(ncclUniqueId) == SHL_COMM_ID_BYTES, "SHL_COMM_ID_BYTES follows ncclUniqueId");
+
+int shl_comm_init(shl_ctx* ctx, const uint8_t* id, int rank, int world) {
+    if (!ctx || !id || world < 1 || rank < 0 || rank >= world) return fail(ctx, SHL_ERR_ARG, "shl_comm_init: bad argument");
+    if (ctx->comm) return fail(ctx, SHL_ERR_ARG, "shl_comm_init: this ctx already has a communicator");
+    if (!g_nccl.load()) return fail(ctx, SHL_ERR_CUDA, g_nccl.why);
+    CU(cudaSetDevice(ctx->device));
+    ncclUniqueId u;
+    memcpy(&u, id, sizeof u);
+    const ncclResult_t r = g_nccl.CommInitRank(&ctx->comm, world, u, rank);
+    if (r != ncclSuccess) { ctx->comm = nullptr; return fail(ctx, SHL_ERR_CUDA, std::string("ncclCommInitRank: ") + g_nccl.GetErrorString(r)); }
+    ctx->comm_rank = rank; ctx->comm_world = world;
+    return SHL_OK;
+}
+int shl_comm_size(shl_ctx* ctx) { return ctx && ctx->comm ? ctx->comm_world : 1; }
+
+int shl_stats_allreduce(shl_ctx* ctx) {
+    if (!ctx) return SHL_ERR_ARG;
+    CU(cudaSetDevice(ctx->device));
+    const int k = ctx->stat_k, k2 = k ^ 1;
+    const size_t bytes = (size_t)ctx->stats_len * 8;
+    CU(cudaEventRecord(ctx->ev_stats_ready[k], ctx->stream));
+    CU(cudaStreamWaitEvent(ctx->comm_stream, ctx->ev_stats_ready[k], 0));
+    if (ctx->comm) {
+        const ncclResult_t r = g_nccl.AllReduce(ctx->d_stats[k], ctx->d_stats[k], ctx->stats_len, ncclUint64, ncclSum, ctx->comm, ctx->comm_stream);
+        if (r != ncclSuccess) return fail(ctx, SHL_ERR_CUDA, std::string("ncclAllReduce: ") + g_nccl.GetErrorString(r));
+    }
+    CU(cudaMemcpyAsync(ctx->h_stats + (size_t)k * ctx->stats_len, ctx->d_stats[k], bytes, cudaMemcpyDeviceToHost, ctx->comm_stream));
+    CU(cudaEventRecord(ctx->ev_stats_done[k], ctx->comm_stream));
+    ctx->stat_last = k;
+    // the other buffer takes the next batches; its previous all-reduce (two calls ago) must be over
+    CU(cudaStreamWaitEvent(ctx->stream, ctx->ev_stats_done[k2], 0));
+    CU(cudaMemsetAsync(ctx->d_stats[k2], 0, bytes, ctx->stream));
+    ctx->stat_k = k2;
+    return SHL_OK;
+}
+int shl_stats_join(shl_ctx* ctx) {
+    if (!ctx) return SHL_ERR_ARG;
+    for (int k = 0; k < 2; k++) CU(cudaStreamWaitEvent(ctx->stream, ctx->ev_stats_done[k], 0));
+    return SHL_OK;
+}
+int shl_stats_fetch(shl_ctx* ctx, uint64_t* out, uint32_t n) {
+    if (!ctx || !out || n > ctx->stats_len) return fail(ctx, SHL_ERR_ARG, "shl_stats_fetch: bad argument");
+    if (ctx->stat_last < 0) return fail(ctx, SHL_ERR_ARG, "shl_stats_fetch: no shl_stats_allreduce yet");
+    CU(cudaEventSynchronize(ctx->ev_stats_done[ctx->stat_last]));
+    memcpy(out, ctx->h_stats + (size_t)ctx->stat_last * ctx->stats_len, (size_t)n * 8);
+    return SHL_OK;
+}
+int shl_comm_allreduce_u64(shl_ctx* ctx, uint64_t* vals, uint32_t n, int op) {
+    if (!ctx || !vals || n == 0 || n > 64 || op < 0 || op > 1) return fail(ctx, SHL_ERR_ARG, "shl_comm_allreduce_u64: bad argument");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));                // doubles as the barrier's "my work is done"
+    CU(cudaStreamSynchronize(ctx->comm_stream));
+    if (!ctx->comm) return SHL_OK;
+    memcpy(ctx->h_scratch, vals, (size_t)n * 8);
+    CU(cudaMemcpyAsync(ctx->d_scratch, ctx->h_scratch, (size_t)n * 8, cudaMemcpyHostToDevice, ctx->comm_stream));
+    const ncclResult_t r = g_nccl.AllReduce(ctx->d_scratch, ctx->d_scratch, n, ncclUint64, op ? ncclMax : ncclSum, ctx->comm, ctx->comm_stream);
+    if (r != ncclSuccess) return fail(ctx, SHL_ERR_CUDA, std::string("ncclAllReduce: ") + g_nccl.GetErrorString(r));
+    CU(cudaMemcpyAsync(ctx->h_scratch, ctx->d_scratch, (size_t)n * 8, cudaMemcpyDeviceToHost, ctx->comm_stream));
+    CU(cudaStreamSynchronize(ctx->comm_stream));
+    memcpy(vals, ctx->h_scratch, (size_t)n * 8);
+    return SHL_OK;
+}
 
 // ------------------------------------------------------------------------------------ corpora
 int shl_corpus_lengths_host(uint64_t seed, uint64_t first, uint64_t n, int kind, uint32_t* len) {
@@ -860,12 +1052,14 @@ __global__ void k_corpus_fill(uint64_t seed, uint64_t first, uint64_t n, int kin
 extern "C" {
 int shl_corpus_lengths_dev(shl_ctx* ctx, uint64_t seed, uint64_t first, uint64_t n, int kind, uint32_t* d_len) {
     if (!ctx || !d_len) return SHL_ERR_ARG;
+    CU(cudaSetDevice(ctx->device));
     if (n) { shl::k_corpus_lengths<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(seed, first, n, kind, d_len); ctx->launches++; }
     CU(cudaGetLastError());
     return SHL_OK;
 }
 int shl_corpus_fill_dev(shl_ctx* ctx, uint64_t seed, uint64_t first, uint64_t n, int kind, const uint64_t* d_off, uint8_t* d_arena) {
     if (!ctx || !d_off || !d_arena) return SHL_ERR_ARG;
+    CU(cudaSetDevice(ctx->device));
     if (n) { shl::k_corpus_fill<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(seed, first, n, kind, d_off, d_arena); ctx->launches++; }
     CU(cudaGetLastError());
     return SHL_OK;
@@ -942,7 +1136,8 @@ extern "C" int shl_place_static(int device, const uint8_t* arena, uint64_t arena
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
         return fail(nullptr, SHL_ERR_NO_DEVICE, "no CUDA device: libshellac_b200 has no CPU fallback");
     if (device < 0 || device >= ndev || device >= kMaxDevices) return fail(nullptr, SHL_ERR_ARG, "shl_place_static: bad device index");
-    CU(cudaSetDevice(device));
+    DeviceGuard guard;                                   // the caller's current device is put back on every way out
+    CU(guard.enter(device));
     // Set-up, once per device and with that device current: ask the runtime where THIS device's
     // copy of the array lives.  The first call on a device does it, so make that first call
     // before any stream capture begins.
@@ -973,7 +1168,8 @@ extern "C" int shl_place_static(int device, const uint8_t* arena, uint64_t arena
     a.out.hist = reinterpret_cast<uint64_t*>(base + kStHist);
     shl::k_place<<<(unsigned)((n + 255) / 256), 256, (size_t)n_hosts * 4, st>>>(a);
     CU(cudaGetLastError());
-    uint64_t bins[SHL_STATIC_MAX_HOSTS];                 // on the stack: no host allocation either
+    uint64_t bins[SHL_STATIC_MAX_HOSTS];                 // on the stack (the success path allocates no host memory either;
+                                                         //  the error paths build a std::string for shl_last_error)
     if (md5) CU(cudaMemcpyAsync(md5, base + kStMd5, n * 16, cudaMemcpyDeviceToHost, st));
     if (hash) CU(cudaMemcpyAsync(hash, base + kStHash, n * 4, cudaMemcpyDeviceToHost, st));
     if (node) CU(cudaMemcpyAsync(node, base + kStNode, n * 4, cudaMemcpyDeviceToHost, st));

@@ -24,6 +24,7 @@
 #pragma once
 #include <cuda_fp16.h>
 #include "shl_device.cuh"
+#include "bitmap_walk.cuh"
 
 namespace shl {
 
@@ -32,7 +33,7 @@ namespace shl {
 #define SHL_OPT_RINGDIR 1             // continuum search through the 4 096-bucket directory
 #endif
 #ifndef SHL_OPT_MINBLOCKS
-#define SHL_OPT_MINBLOCKS 8           // resident blocks per SM the register allocation aims at
+#define SHL_OPT_MINBLOCKS 6           // resident blocks per SM the register allocation aims at
 #endif
 #ifndef SHL_OPT_BATCH
 #define SHL_OPT_BATCH 2               // header lines whose value peeks are in flight together
@@ -194,7 +195,7 @@ __device__ __forceinline__ void finalize_headers(const uint8_t* m, int L, int bo
 }
 
 // ----------------------------------------------------------------------------------- scan: one message, one lane
-struct LaneScan { int idx, T, sp1, sp2; uint32_t n_c, n_s, s_skip; bool ovf, bad; };
+struct LaneScan { int idx, T; uint32_t n_c, n_s, s_skip; bool ovf, bad; };
 
 // cr[k * 32] / sp[k * 32]: this lane's slots of the warp's position lists (u16, lane-interleaved).
 // 0xFFFF in each 16-bit half of x that equals the matching half of pat.  The halves are compared
@@ -252,7 +253,7 @@ __device__ __forceinline__ uint32_t vec_events(const uint32_t c, const uint4& v)
 // CRLF, of the ':' of every ": "); which separator belongs to which line is worked out afterwards
 // from the positions (count_lines), when the lanes are converged again.
 struct ScanState {
-    int T, last_cr, sp1, sp2;
+    int T, last_cr;
     uint32_t n_c, n_s;
     uint32_t s_prev, s_skip, bad;      // ": " listed before the last CRLF / inside the first line; some line did not hold exactly one
 };
@@ -269,13 +270,6 @@ __device__ __forceinline__ void scan_step(const uint4& v, const uint32_t c, cons
         ev &= mhi & ~mlo;
     }
     uint32_t sb = ev & 0x55555555u, cb = ev & 0xaaaaaaaau;
-    if (st.n_c == 0u) {                            // still on the first line: note its first two spaces
-        uint32_t z = mask16(eqf(v.x, K.sp, K), eqf(v.y, K.sp, K), eqf(v.z, K.sp, K), eqf(v.w, K.sp, K));
-        if (p < 0 || p + 16 > L) z &= rng16(-p, L - p);
-        if (cb) z &= below(max(((__ffs(cb) - 1) >> 1) - 1, 0));        // spaces before the line's CR only
-        if (z && st.sp1 < 0) { st.sp1 = p + __ffs(z) - 1; z &= z - 1u; }
-        if (z && st.sp1 >= 0 && st.sp2 < 0) st.sp2 = p + __ffs(z) - 1;
-    }
     const int q = p - 1;
     const uint32_t sb0 = sb, n_s0 = st.n_s;
     if (sb) {                                      // the common vector holds at most one ": " ...
@@ -321,7 +315,7 @@ __device__ __forceinline__ void scan_lists(const uint8_t* m, const int L, uint16
     const uint4* vp = reinterpret_cast<const uint4*>(m - lead);
     const int nsec = (lead + L + 31) >> 5;         // 32-byte sectors that hold message bytes
     int p = -lead;                                 // message position of byte 0 of the current sector
-    ScanState st; st.T = -1; st.last_cr = -4; st.sp1 = st.sp2 = -1; st.n_c = st.n_s = st.s_prev = st.s_skip = st.bad = 0u;
+    ScanState st; st.T = -1; st.last_cr = -4; st.n_c = st.n_s = st.s_prev = st.s_skip = st.bad = 0u;
     uint32_t c = 0u;                               // word before the current vector (masked off in sector 0)
     uint4 a0 = __ldg(vp), b0 = __ldg(vp + 1), a1, b1;
     a1 = b1 = make_uint4(0u, 0u, 0u, 0u);
@@ -333,7 +327,7 @@ __device__ __forceinline__ void scan_lists(const uint8_t* m, const int L, uint16
         if (st.T >= 0) break;
         c = b0.w; a0 = a1; b0 = b1;
     }
-    o.T = st.T; o.n_c = st.n_c; o.n_s = st.n_s; o.sp1 = st.sp1; o.sp2 = st.sp2;
+    o.T = st.T; o.n_c = st.n_c; o.n_s = st.n_s;
     o.idx = st.n_c ? (int)cr[0] : -1;
     o.s_skip = st.s_skip; o.bad = st.bad != 0u;
     o.ovf = st.n_c > (uint32_t)kCrCap || st.n_s > (uint32_t)kSepCap;       // the lists are incomplete: scalar path
@@ -365,26 +359,63 @@ __device__ __forceinline__ uint32_t count_lines(const uint16_t* cr, const uint16
 // The 32 messages of a group usually lie back to back in the arena (that is how every packer in
 // this repo, and a recv() loop, lays them out).  Then the warp does not scan 32 messages in 32
 // lanes, it scans ONE span of bytes with 32 lanes:
-//   phase A  lane l classifies bytes [1024 r + 32 l, +32) of the span in row r (fully coalesced
-//            loads, every lane busy until the last row, no per-message edges), and the set bits
-//            are compacted, in position order, into two flat u16 lists for the whole group
-//            (positions relative to the span) with one warp prefix sum per row;
-//   phase B  lane j finds message j's slice of the lists by binary search and walks its CRLFs
-//            (first line end, CRLFCRLF, one ": " per line) with all lanes doing the same thing.
-// A group that does not qualify (unordered or overlapping messages, a span over kSpanMax, more
-// events than the lists hold) is scanned message-per-lane by scan_lists, with identical results.
-constexpr uint32_t kSpanMax = 32768u;
-constexpr uint32_t kCrFlat = kCrCap * 32, kSepFlat = kSepCap * 32;
+//   phase A  lane l classifies bytes [1024 r + 32 l, +32) of the span in row r (fully coalesced,
+//            every lane busy until the last row, no per-message edges) and stores the result as
+//            two 32-bit words, "a CRLF starts here" / "a ': ' starts here", one bit per byte, in
+//            shared memory: 2 bits per span byte, no compaction, no prefix sums;
+//   phase B  lane j reads message j's framing off those bitmaps (bitmap_walk.cuh): first line end,
+//            CRLFCRLF, and "one ': ' per line" as an alternation check with a carry chain.
+// A group that does not qualify (unordered or overlapping messages, a span over kSpanMax) is
+// scanned message-per-lane by scan_lists, with identical results.
+#ifndef SHL_OPT_SPANMAX
+#define SHL_OPT_SPANMAX 20480         // bytes of span a warp keeps bitmaps for (config 2: 16.4 KiB +- 0.4)
+#endif
+constexpr uint32_t kSpanMax = SHL_OPT_SPANMAX;
+constexpr uint32_t kBmWords = kSpanMax / 32u + 2u;         // + the straddling word + one zero word behind the last
+static_assert(kBmWords * 8u >= (kCrCap * 32u + 2u + kSepCap * 32u + 2u) * 2u, "the per-lane lists share the bitmaps' storage");
 
-// lists the events of span[0:nbytes) (A0 is 32-byte aligned); false = the lists overflowed
-__device__ __forceinline__ bool group_list_events(const uint8_t* A0, const uint32_t nbytes, uint16_t* crl, uint16_t* sepl,
-                                                  const int lane, uint32_t& n_c_tot, uint32_t& n_s_tot) {
-    uint32_t base_c = 0u, base_s = 0u, prev_last = 0u;
+// Event nibbles of one 32-bit word w (pv = the word BEFORE it in memory) for the four byte pairs
+// that END inside w: bit j = a ": " starts at byte j - 1 of w, bit 4 + j = a CRLF starts there
+// (j = 0 is the pair that straddles pv and w).  HSET2.BF gives 1.0 per matching half, four HFMA2
+// add them up with power-of-two weights on top of 1024.0, whose fp16 mantissa then IS the bit
+// field (low half: pairs -1 and 0, high half: pairs 1 and 2, disjoint bits); x * 0x10001 has
+// lo + hi in byte 2.  The kernel is bound by the integer ALU pipe, so the gather runs on the
+// half-precision FMA pipe on purpose.
+__device__ __forceinline__ uint32_t pair_nibbles(uint32_t pv, uint32_t w) {
+    const uint32_t sh = __funnelshift_r(pv, w, 24);
+    const uint32_t kCR = 0x0A0D0A0Du, kSEP = 0x203A203Au;
+    const uint32_t kS1 = 0x44003C00u, kS2 = 0x48004000u, kC1 = 0x54004C00u, kC2 = 0x58005000u, kM = 0x64006400u;   // (1,4) (2,8) (16,64) (32,128) (1024,1024)
+#define SHL_H2(x) (*reinterpret_cast<const __half2*>(&(x)))
+    __half2 acc = __hfma2(__heq2(SHL_H2(sh), SHL_H2(kSEP)), SHL_H2(kS1), SHL_H2(kM));
+    acc = __hfma2(__heq2(SHL_H2(sh), SHL_H2(kCR)), SHL_H2(kC1), acc);
+    acc = __hfma2(__heq2(SHL_H2(w), SHL_H2(kSEP)), SHL_H2(kS2), acc);
+    acc = __hfma2(__heq2(SHL_H2(w), SHL_H2(kCR)), SHL_H2(kC2), acc);
+#undef SHL_H2
+    return *reinterpret_cast<const uint32_t*>(&acc) * 0x00010001u;
+}
+
+// The two bitmap words of the 32 bytes (va, vb), c = the word before them.  Words 0, 2, 4, 6 and
+// 1, 3, 5, 7 are packed separately so that one shift and one LOP3 per bitmap interleave their
+// nibbles back into position order.
+__device__ __forceinline__ bm2 window_bits(const uint32_t c, const uint4& va, const uint4& vb) {
+    const uint32_t e0 = pair_nibbles(c, va.x), e1 = pair_nibbles(va.x, va.y), e2 = pair_nibbles(va.y, va.z), e3 = pair_nibbles(va.z, va.w);
+    const uint32_t e4 = pair_nibbles(va.w, vb.x), e5 = pair_nibbles(vb.x, vb.y), e6 = pair_nibbles(vb.y, vb.z), e7 = pair_nibbles(vb.z, vb.w);
+    const uint32_t ev = __byte_perm(__byte_perm(e0, e2, 0x0062), __byte_perm(e4, e6, 0x0062), 0x5410);    // byte 2 of each
+    const uint32_t od = __byte_perm(__byte_perm(e1, e3, 0x0062), __byte_perm(e5, e7, 0x0062), 0x5410);
+    bm2 r;
+    r.y = (ev & 0x0f0f0f0fu) | ((od << 4) & 0xf0f0f0f0u);
+    r.x = ((ev >> 4) & 0x0f0f0f0fu) | (od & 0xf0f0f0f0u);
+    return r;
+}
+
+// bitmaps of span[0:nbytes) (A0 is 32-byte aligned, nbytes <= kSpanMax)
+__device__ __forceinline__ void group_bitmaps(const uint8_t* A0, const uint32_t nbytes, bm2* bm, const int lane) {
+    uint32_t prev_last = 0u;
     uint32_t boff = (uint32_t)lane * 32u;
     uint4 va = make_uint4(0u, 0u, 0u, 0u), vb = va;
     if (boff < nbytes) { va = __ldg(reinterpret_cast<const uint4*>(A0 + boff)); vb = __ldg(reinterpret_cast<const uint4*>(A0 + boff + 16)); }
-    bool fits = true;
-    for (; boff - (uint32_t)lane * 32u < nbytes; boff += 1024u) {          // warp-uniform trip count
+    uint32_t w = (uint32_t)lane;
+    for (; boff - (uint32_t)lane * 32u < nbytes; boff += 1024u, w += 32u) {      // warp-uniform trip count
         uint4 na = make_uint4(0u, 0u, 0u, 0u), nb = na;
         if (boff + 1024u < nbytes) {                                        // next row in flight
             na = __ldg(reinterpret_cast<const uint4*>(A0 + boff + 1024u)); nb = __ldg(reinterpret_cast<const uint4*>(A0 + boff + 1040u));
@@ -392,128 +423,29 @@ __device__ __forceinline__ bool group_list_events(const uint8_t* A0, const uint3
         uint32_t c = __shfl_up_sync(SHL_FULL, vb.w, 1);
         if (lane == 0) c = prev_last;
         prev_last = __shfl_sync(SHL_FULL, vb.w, 31);
-        const uint32_t ev0 = vec_events(c, va), ev1 = vec_events(va.w, vb);
-        uint32_t cb0 = ev0 & 0xaaaaaaaau, sb0 = ev0 & 0x55555555u, cb1 = ev1 & 0xaaaaaaaau, sb1 = ev1 & 0x55555555u;
-        const uint32_t n0c = (uint32_t)__popc(cb0), n0s = (uint32_t)__popc(sb0);
-        const uint32_t cnt = (n0c + (uint32_t)__popc(cb1)) | ((n0s + (uint32_t)__popc(sb1)) << 16);
-        uint32_t inc = cnt;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(SHL_FULL, inc, d); if (lane >= d) inc += t; }
-        const uint32_t tot = __shfl_sync(SHL_FULL, inc, 31);
-        if (base_c + (tot & 0xffffu) > kCrFlat || base_s + (tot >> 16) > kSepFlat) { fits = false; break; }
-        // my slots: the first vector's events, then the second's
-        uint32_t ic0 = base_c + ((inc - cnt) & 0xffffu), is0 = base_s + ((inc - cnt) >> 16);
-        uint32_t ic1 = ic0 + n0c, is1 = is0 + n0s;
-        const uint32_t q0 = boff - 1u, q1 = boff + 15u;
-        // A vector rarely holds more than one event of a kind: the first of each kind is written
-        // without a branch (a lane with none writes to the spare slot behind the list), and one
-        // test covers what is left (the second CRLF of a CRLFCRLF, short lines).
-#define SHL_PUT_FIRST(bits, list, spare, idx, q) { const int b_ = __ffs(bits) - 1; const bool h_ = (bits) != 0u; \
-            (list)[h_ ? (idx) : (spare)] = (uint16_t)((q) + (uint32_t)(b_ >> 1)); (idx) += h_ ? 1u : 0u; (bits) &= (bits) - 1u; }
-        SHL_PUT_FIRST(cb0, crl, kCrFlat, ic0, q0)
-        SHL_PUT_FIRST(cb1, crl, kCrFlat, ic1, q1)
-        SHL_PUT_FIRST(sb0, sepl, kSepFlat, is0, q0)
-        SHL_PUT_FIRST(sb1, sepl, kSepFlat, is1, q1)
-#undef SHL_PUT_FIRST
-        if (cb0 | cb1 | sb0 | sb1) {
-            while (cb0) { const int b = __ffs(cb0) - 1; cb0 &= cb0 - 1u; crl[ic0++] = (uint16_t)(q0 + (uint32_t)(b >> 1)); }
-            while (cb1) { const int b = __ffs(cb1) - 1; cb1 &= cb1 - 1u; crl[ic1++] = (uint16_t)(q1 + (uint32_t)(b >> 1)); }
-            while (sb0) { const int b = __ffs(sb0) - 1; sb0 &= sb0 - 1u; sepl[is0++] = (uint16_t)(q0 + (uint32_t)(b >> 1)); }
-            while (sb1) { const int b = __ffs(sb1) - 1; sb1 &= sb1 - 1u; sepl[is1++] = (uint16_t)(q1 + (uint32_t)(b >> 1)); }
-        }
-        base_c += tot & 0xffffu; base_s += tot >> 16;
+        bm[w] = window_bits(c, va, vb);
         va = na; vb = nb;
     }
-    n_c_tot = base_c; n_s_tot = base_s;
-    return fits;
-}
-
-// first index i in list[0:n) with list[i] >= key
-__device__ __forceinline__ uint32_t list_lower_bound(const uint16_t* list, const uint32_t n, const uint32_t key) {
-    uint32_t lo = 0u, hi = n;
-    while (lo < hi) {
-        const uint32_t mid = (lo + hi) >> 1;
-        if ((uint32_t)list[mid] < key) lo = mid + 1u; else hi = mid;
-    }
-    return lo;
-}
-
-// What phase B hands to the epilogue for one message.
-struct GroupWalk {
-    int idx, T;                        // message-relative positions of the first line's CR / the CR that ends the header block
-    uint32_t n_c;                      // CRLFs up to and including T's (header lines + 1)
-    uint32_t ic0, js0;                 // list index of the first line's CR / of the first header line's ": "
-    uint32_t first_bad, err;           // first header line without exactly one ": " (or 0xffffffff) and its error code
-};
-
-// message [s0, s0 + L) of the span: HttpParser.parse's framing decisions from the two lists
-__device__ __forceinline__ void group_walk(const uint16_t* crl, const uint16_t* sepl, const uint32_t n_c_tot, const uint32_t n_s_tot,
-                                           const uint32_t s0, const int L, GroupWalk& o) {
-    o.idx = o.T = -1; o.n_c = 0u; o.first_bad = 0xffffffffu; o.err = 0u;
-    const uint32_t lim = s0 + (uint32_t)max(L, 2) - 2u;                // last position a pair of this message may start at
-    uint32_t k = list_lower_bound(crl, n_c_tot, s0);
-    uint32_t js = list_lower_bound(sepl, n_s_tot, s0);
-    o.ic0 = k; o.js0 = js;
-    if (L < 2 || k >= n_c_tot) return;
-    uint32_t prev = crl[k];
-    if (prev > lim) return;
-    o.idx = (int)(prev - s0); o.n_c = 1u;
-    while (js < n_s_tot && (uint32_t)sepl[js] < prev) js++;            // ": " inside the first line are not separators
-    o.js0 = js;
-    // Line i (i = 0, 1, ...) must own separator js + i and no other: the loop only ANDs "it lies
-    // inside the line" (a second ": " in a line shows up as the next line's separator lying before
-    // that line); which line is the offender is worked out afterwards, in the rare bad block.
-    uint32_t ok = 1u;
-    const uint32_t ic0 = k;
-    for (k++; k < n_c_tot; k++) {
-        const uint32_t pos = crl[k];
-        if (pos > lim) break;
-        if (pos == prev + 2u && o.n_c >= 2u) { o.T = (int)(prev - s0); break; }       // empty line after the first line: CRLFCRLF
-        const uint32_t si = js + o.n_c - 1u;
-        const uint32_t sv = si < n_s_tot ? (uint32_t)sepl[si] : 0xffffffffu;
-        ok &= (sv > prev ? 1u : 0u) & (sv < pos ? 1u : 0u);
-        prev = pos; o.n_c++;
-    }
-    if (o.T < 0) return;
-    {
-        const uint32_t si = js + o.n_c - 1u;                            // the one after the last line's: beyond the block, or absent
-        const uint32_t sv = si < n_s_tot ? (uint32_t)sepl[si] : 0xffffffffu;
-        ok &= sv > prev ? 1u : 0u;
-    }
-    if (ok) return;
-    uint32_t cur = js < n_s_tot ? (uint32_t)sepl[js] : 0xffffffffu;
-    for (uint32_t line = 0; line + 1u < o.n_c; line++) {
-        const uint32_t end = crl[ic0 + line + 1u];
-        const uint32_t nxt = js + 1u < n_s_tot ? (uint32_t)sepl[js + 1u] : 0xffffffffu;
-        if (cur > end) { o.first_bad = line; o.err = SHL_E_HDR_NO_SEP; return; }
-        if (nxt < end) { o.first_bad = line; o.err = SHL_E_HDR_MULTI_SEP; return; }
-        cur = nxt; js++;
-    }
-}
-
-// the first two spaces of m[0:idx) (the scan of the per-lane path notes them as it goes)
-__device__ __forceinline__ void first_two_spaces(const uint8_t* m, const int idx, const SwarK& K, int& sp1, int& sp2) {
-    const int lead = (int)(reinterpret_cast<uintptr_t>(m) & 15);
-    const uint4* vp = reinterpret_cast<const uint4*>(m - lead);
-    sp1 = sp2 = -1;
-    for (int p = -lead; p < idx && sp2 < 0; p += 16, vp++) {
-        const uint4 v = __ldg(vp);
-        uint32_t z = mask16(eqf(v.x, K.sp, K), eqf(v.y, K.sp, K), eqf(v.z, K.sp, K), eqf(v.w, K.sp, K));
-        if (p < 0 || p + 16 > idx) z &= rng16(-p, idx - p);
-        if (z && sp1 < 0) { sp1 = p + __ffs(z) - 1; z &= z - 1u; }
-        if (z && sp1 >= 0 && sp2 < 0) sp2 = p + __ffs(z) - 1;
-    }
+    if (lane == 0) { bm2 z; z.x = z.y = 0u; bm[w] = z; }                        // the word behind the last row
 }
 
 // ----------------------------------------------------------------------------------- epilogue helpers
-// Canonical request line  METHOD SP URL SP "HTTP/1.x" CRLF  (no other space, no trailing blank):
-// fills the first-line fields and returns true; anything else goes to first_line_scalar.
-__device__ __forceinline__ bool first_line_fast(const uint8_t* m, const int idx, const int sp1, const int sp2, Msg& r, bool& get_or_head) {
-    // sp1 / sp2 are the first two spaces of the line (noted by the scan); the third part must be
-    // exactly the 8 bytes "HTTP/1.0" or "HTTP/1.1", which also rules out a trailing blank.
-    if (sp1 < 0 || sp2 <= sp1 || idx - sp2 - 1 != 8) return false;
-    const uint32_t w0 = ld32u(m + sp2 + 1), w1 = ld32u(m + sp2 + 5), f4 = ld32u(m);
-    if (w0 != 0x50545448u || (w1 != 0x312E312Fu && w1 != 0x302E312Fu)) return false;
+// Canonical request line  METHOD SP URL SP "HTTP/1.x" CRLF  with a method of at most 7 bytes:
+// everything is decided from the line's first 8 and last 9 bytes (five independent loads, one
+// round trip), EXCEPT that the URL must not hold a space; the caller checks that while it fetches
+// the URL's words for the MD5 (md5_key_t<true>) and falls back to first_line_scalar like for any
+// other shape.  Fills the first-line fields and returns true when the shape holds.
+__device__ __forceinline__ bool first_line_canon(const uint8_t* m, const int idx, Msg& r, bool& get_or_head) {
+    if (idx < 14) return false;                                           // "X / HTTP/1.1" and shorter: the scalar path is exact
+    const uint64_t head = ld64u(m), tail = ld64u(m + idx - 8);
+    const uint32_t sp2c = ldb(m + idx - 9);
+    const uint32_t f4 = (uint32_t)head, w0 = (uint32_t)tail, w1 = (uint32_t)(tail >> 32);
+    if (w0 != 0x50545448u || (w1 != 0x312E312Fu && w1 != 0x302E312Fu) || sp2c != ' ') return false;
+    const uint32_t z0 = has_zero_byte(f4 ^ 0x20202020u), z1 = has_zero_byte((uint32_t)(head >> 32) ^ 0x20202020u);
+    if (!(z0 | z1)) return false;                                         // no space in the first 8 bytes
+    const int sp1 = z0 ? ((__ffs(z0) - 1) >> 3) : 4 + ((__ffs(z1) - 1) >> 3);
+    const int sp2 = idx - 9;
+    if (sp2 <= sp1) return false;
     if ((f4 & 0xffffu) == 0x5448u && sp1 >= 2) return false;            // a.startswith('HT'): a response
     r.sp1 = (uint32_t)sp1; r.sp2 = (uint32_t)sp2; r.fl_end = (uint32_t)idx; r.slash = (uint32_t)(sp2 + 5);
     r.status = (r.status & ~SHL_F_VERSION_MASK) | ((w1 >> 24) == '1' ? 1u << SHL_F_VERSION_SHIFT : 0u) | SHL_F_FIRST_LINE_DONE;
@@ -531,11 +463,108 @@ __device__ __noinline__ int find_term_scalar(const uint8_t* m, int from, int L) 
     return -1;
 }
 
+// ----------------------------------------------------------------------------------- records
+// One header line [ls, end) with its separator at sep: strip the value (HttpParser.py:329; c0 / c1
+// are the value's first and last byte, already loaded), store the record, remember the line if
+// its key has the length of one of the two names the header state cares about (:194-197).
+struct NameCand { uint32_t n14, n17, lo14, hi14, lo17, hi17; };       // first record of each length, as stored
+__device__ __forceinline__ void put_record(const uint8_t* m, shl_hdr_span* out, const uint32_t k, const int ls, const int sep,
+                                           const int end, const uint32_t c0, const uint32_t c1, NameCand& nc) {
+    int vs = sep + 2, ve = end;
+    if (is_ws(c0) || is_ws(c1)) {
+        while (vs < ve && is_ws(ldb(m + vs))) vs++;
+        while (ve > vs && is_ws(ldb(m + ve - 1))) ve--;
+    }
+    const int klen = sep - ls;
+    const uint32_t lo = (uint32_t)ls | ((uint32_t)klen << 16), hi = (uint32_t)vs | ((uint32_t)(ve - vs) << 16);
+    *reinterpret_cast<uint2*>(out + k) = make_uint2(lo, hi);
+    if (klen == 14) { if (!nc.n14) { nc.lo14 = lo; nc.hi14 = hi; } nc.n14++; }
+    if (klen == 17) { if (!nc.n17) { nc.lo17 = lo; nc.hi17 = hi; } nc.n17++; }
+}
+// The candidates' names are compared after the loop (one out-of-line compare per candidate
+// instead of a byte load in every iteration).  A second candidate of the same length is rare:
+// then the records just written are read back.
+__device__ __noinline__ void note_names_rescan(const uint8_t* m, const shl_hdr_span* out, const uint32_t nh, WellKnown& wk) {
+    wk.n_te = wk.n_cl = 0;
+    for (uint32_t k = 0; k < nh; k++) {
+        const shl_hdr_span rec = out[k];
+        const uint32_t vs = rec.val_off, ve = (uint32_t)rec.val_off + rec.val_len;
+        if (rec.key_len == 14 && span_eq_lower(m, rec.key_off, rec.key_off + 14, "content-length")) { if (!wk.n_cl) { wk.cl_vs = vs; wk.cl_ve = ve; } wk.n_cl++; }
+        if (rec.key_len == 17 && span_eq_lower(m, rec.key_off, rec.key_off + 17, "transfer-encoding")) { if (!wk.n_te) { wk.te_vs = vs; wk.te_ve = ve; } wk.n_te++; }
+    }
+}
+__device__ __forceinline__ void note_names(const uint8_t* m, const shl_hdr_span* out, const uint32_t nh, const NameCand& nc, WellKnown& wk) {
+    if (nc.n14 > 1u || nc.n17 > 1u) { note_names_rescan(m, out, nh, wk); return; }
+    if (nc.n14) {
+        const int ko = (int)(nc.lo14 & 0xffffu);
+        if (span_eq_lower(m, ko, ko + 14, "content-length")) { wk.cl_vs = nc.hi14 & 0xffffu; wk.cl_ve = (nc.hi14 & 0xffffu) + (nc.hi14 >> 16); wk.n_cl = 1; }
+    }
+    if (nc.n17) {
+        const int ko = (int)(nc.lo17 & 0xffffu);
+        if (span_eq_lower(m, ko, ko + 17, "transfer-encoding")) { wk.te_vs = nc.hi17 & 0xffffu; wk.te_ve = (nc.hi17 & 0xffffu) + (nc.hi17 >> 16); wk.n_te = 1; }
+    }
+}
+
+// Group-span path: line k's separator and end are the next two events of the message's block in
+// the bitmaps (they alternate in a validated block).  kB lines per round; the round after it is
+// located and its byte peeks are issued before this one is written (an L2 round trip per round
+// would be exposed otherwise).
+#ifndef SHL_OPT_EMIT
+#define SHL_OPT_EMIT 1
+#endif
+__device__ __forceinline__ void emit_records_bm(const uint8_t* m, const bm2* bm, const uint32_t q_idx, const int qsub, const int h0,
+                                                const uint32_t nh, shl_hdr_span* out, WellKnown& wk) {
+    NameCand nc; nc.n14 = nc.n17 = nc.lo14 = nc.hi14 = nc.lo17 = nc.hi17 = 0u;
+    constexpr int kB = SHL_OPT_EMIT;
+    if (nh) {
+        EvCursor ec;
+        evc_init(ec, bm, q_idx);
+        struct Round { int sep[kB], end[kB]; uint32_t c0[kB], c1[kB]; };
+        auto fetch = [&](const uint32_t k, Round& p) {
+#pragma unroll
+            for (int j = 0; j < kB; j++) {
+                p.sep[j] = p.end[j] = 0; p.c0[j] = p.c1[j] = 'x';
+                if (k + (uint32_t)j < nh) {
+                    p.sep[j] = (int)evc_pop(ec, bm) - qsub; p.end[j] = (int)evc_pop(ec, bm) - qsub;
+#ifndef SHL_EXP_NOPEEK
+                    if (p.sep[j] + 2 < p.end[j]) { p.c0[j] = ldb(m + p.sep[j] + 2); p.c1[j] = ldb(m + p.end[j] - 1); }
+#endif
+                }
+            }
+        };
+        Round cur, nxt;
+        fetch(0u, cur);
+        int ls = h0;
+        for (uint32_t k = 0; k < nh; k += kB) {
+            fetch(k + kB, nxt);
+#pragma unroll
+            for (int j = 0; j < kB; j++) {
+                if (k + (uint32_t)j < nh) { put_record(m, out, k + j, ls, cur.sep[j], cur.end[j], cur.c0[j], cur.c1[j], nc); ls = cur.end[j] + 2; }
+            }
+            cur = nxt;
+        }
+    }
+    note_names(m, out, nh, nc, wk);
+}
+// Per-lane path: the positions come from the lane's slots of the interleaved lists.
+__device__ __noinline__ void emit_records_lists(const uint8_t* m, const uint16_t* cr, const uint16_t* spp, const int h0,
+                                                const uint32_t nh, shl_hdr_span* out, WellKnown& wk) {
+    NameCand nc; nc.n14 = nc.n17 = nc.lo14 = nc.hi14 = nc.lo17 = nc.hi17 = 0u;
+    int ls = h0;
+    for (uint32_t k = 0; k < nh; k++) {
+        const int sep = (int)spp[k * 32], end = (int)cr[(k + 1u) * 32];
+        uint32_t c0 = 'x', c1 = 'x';
+        if (sep + 2 < end) { c0 = ldb(m + sep + 2); c1 = ldb(m + end - 1); }
+        put_record(m, out, k, ls, sep, end, c0, c1, nc);
+        ls = end + 2;
+    }
+    note_names(m, out, nh, nc, wk);
+}
+
 // ----------------------------------------------------------------------------------- kernel
 template <bool kPlace, bool kFull>     // kFull: 32 messages per warp (compile-time), else a.group of them
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_route(const RouteArgs a) {
-    __shared__ uint16_t s_cr[kWarpsPerBlock][kCrCap * 32 + 2];       // + a spare slot for branch-free writes
-    __shared__ uint16_t s_sp[kWarpsPerBlock][kSepCap * 32 + 2];
+    __shared__ bm2 s_bm[kWarpsPerBlock][kBmWords];             // the group's bitmaps; the per-lane path keeps its lists here
     __shared__ uint32_t s_codes[64];
     extern __shared__ uint32_t s_hist[];                       // kPlace: n_hosts bins (when they fit)
 
@@ -548,20 +577,26 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
 
     // (A block-level counting sort of the messages by scan length, so that the lanes of a warp
     // finish together, was tried here: 1.6 % faster and one more thing to get wrong.  Not kept.)
-    {
-        const uint32_t gsz = kFull ? (uint32_t)kGroup : a.group;
-        const uint64_t mine = ((uint64_t)blockIdx.x * kWarpsPerBlock + warp) * gsz + lane;
+    // A warp takes groups blockIdx * warps + warp, + gridDim * warps, ...: the grid is sized to what
+    // the machine holds at once (api.cu), so the per-block set-up and the tail where finished warps
+    // wait for the block's slowest are paid once per resident block, not once per four groups.
+    const uint32_t gsz = kFull ? (uint32_t)kGroup : a.group;
+    const uint64_t n_groups = (a.n + gsz - 1u) / gsz;
+    for (uint64_t grp = (uint64_t)blockIdx.x * kWarpsPerBlock + warp; grp < n_groups; grp += (uint64_t)gridDim.x * kWarpsPerBlock) {
+        __syncwarp();                                          // every lane is done with the previous group's bitmaps
+        const uint64_t mine = grp * gsz + lane;
         const bool have = (kFull || (uint32_t)lane < gsz) && mine < a.n;
         const uint64_t my_off = have ? a.off[mine] : 0ull;
         const int L = have ? (int)min(a.len[mine], 0x7fffffc0u) : 0;
         const uint8_t* m = a.arena + my_off;
-        uint16_t* cr = &s_cr[warp][lane];
-        uint16_t* sp = &s_sp[warp][lane];
+        const bm2* bm = s_bm[warp];
+        uint16_t* cr = reinterpret_cast<uint16_t*>(s_bm[warp]) + lane;            // per-lane path: lane-interleaved lists
+        uint16_t* sp = cr + kCrCap * 32 + 2;
         const bool force = a.force_scalar != 0;
 
         // ---- scan: the whole group as one span of bytes when its messages lie in order ...
-        LaneScan sc; sc.idx = sc.T = sc.sp1 = sc.sp2 = -1; sc.n_c = sc.n_s = sc.s_skip = 0u; sc.ovf = sc.bad = false;
-        GroupWalk gw; gw.idx = gw.T = -1; gw.n_c = gw.ic0 = gw.js0 = gw.err = 0u; gw.first_bad = 0xffffffffu;
+        LaneScan sc; sc.idx = sc.T = -1; sc.n_c = sc.n_s = sc.s_skip = 0u; sc.ovf = sc.bad = false;
+        BmWalk gw; gw.idx = gw.T = -1; gw.n_c = gw.q_idx = gw.bad = 0u;
         uint32_t s0 = 0u;                                      // my message's position in the span
         bool coal = false;
         if (!force && __shfl_sync(SHL_FULL, (int)have, 0)) {
@@ -572,22 +607,16 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
             const bool ok = !have || ((lane == 0 || m >= prev_end) && (uint64_t)(my_end - A0) <= (uint64_t)kSpanMax);
             if (__all_sync(SHL_FULL, ok)) {
                 const uint32_t nbytes = __reduce_max_sync(SHL_FULL, have ? (uint32_t)(my_end - A0) : 0u);
-                uint32_t nct = 0u, nst = 0u;
-                coal = group_list_events(A0, nbytes, s_cr[warp], s_sp[warp], lane, nct, nst);
+                group_bitmaps(A0, nbytes, s_bm[warp], lane);
                 __syncwarp();
-                if (coal) {
-                    s0 = (uint32_t)(m - A0);
-                    if (have) group_walk(s_cr[warp], s_sp[warp], nct, nst, s0, L, gw);
-                    sc.idx = gw.idx; sc.T = gw.T; sc.n_c = gw.n_c;
-                    if (gw.idx >= 0) first_two_spaces(m, gw.idx, K, sc.sp1, sc.sp2);
-                }
+                coal = true;
+                s0 = (uint32_t)(m - A0);
+                if (have) bm_walk(bm, s0, L, gw);
+                sc.idx = gw.idx; sc.T = gw.T; sc.n_c = gw.n_c;
             }
         }
         // ... else message per lane (lanes diverge on their own events; nothing heavy happens in here)
         if (!coal && L > 0) scan_lists(m, L, cr, sp, K, sc);
-        const uint16_t* crp = coal ? &s_cr[warp][gw.ic0] : cr;     // line k ends at crp[(k + 1) * lstride] - lsub
-        const int lstride = coal ? 1 : 32;
-        const int lsub = coal ? (int)s0 : 0;
 
         // ---- first line, header block bounds, line count
         Msg r;
@@ -596,6 +625,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
         r.status_code = 0; r.content_len = 0;
         WellKnown wk; wk.n_te = wk.n_cl = 0; wk.te_vs = wk.te_ve = wk.cl_vs = wk.cl_ve = 0;
         uint32_t n_hdr = 0, hdr_err = 0, s_skip = 0;
+        uint32_t hash0 = 0u;
+        bool hashed = false;                                   // the digest of this message's URL is stored, hash0 is its first word
         int h0 = 0, T = -1;
         bool get_or_head = false, slow = false, hdr_state = false;   // hdr_state: the header block will be tokenised
         if (L == 0) r.status |= SHL_S_EMPTY;
@@ -606,7 +637,28 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
             else {
                 r.first_line_len = (uint32_t)(idx + 2);
                 uint32_t fl_code = 0;
-                if (force || sc.ovf || !first_line_fast(m, idx, sc.sp1, sc.sp2, r, get_or_head)) {
+                // canonical request line: fields from its two ends; its URL words are fetched once,
+                // for the digest and for "no space inside" together (placement is speculative here:
+                // it is committed at the end, if the message turns out routable)
+                bool canon = !force && !sc.ovf;
+                if (canon) {
+                    Msg t = r; bool goh = false;
+                    canon = first_line_canon(m, idx, t, goh);
+                    if (canon) {
+                        const uint8_t* url = m + t.sp1 + 1u;
+                        const uint32_t ulen = t.sp2 - t.sp1 - 1u;
+                        if (kPlace) {
+                            uint32_t hh[4];
+                            canon = md5_key_t<true>(url, ulen, hh) == 0u;
+                            if (canon) {       // stored now, withdrawn at the end if the message is not routable after all
+                                if (a.place.md5) reinterpret_cast<uint4*>(a.place.md5)[mine] = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+                                hash0 = hh[0]; hashed = true;
+                            }
+                        } else canon = !span_has_space(url, ulen);
+                        if (canon) { r = t; get_or_head = goh; }
+                    }
+                }
+                if (!canon) {
                     Msg t = r; bool goh = false;   // the cold path may keep its copy in local memory
                     fl_code = first_line_scalar(m, idx, t, goh);
                     r = t; get_or_head = goh;
@@ -627,13 +679,15 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
                             wk = w2; n_hdr = n2;
                         } else {
                             // lines before the first one that does not hold exactly one ": " are the
-                            // records; line k's separator is the (s_skip + k)-th listed one
-                            // (the scan kept a flag while it listed them; only a block that
-                            // tripped it is walked again to find the offender)
+                            // records (the scan kept a flag; only a block that tripped it is walked
+                            // again to find the offender)
                             if (coal) {
-                                const uint32_t n_lines = gw.n_c - 1u;
-                                n_hdr = min(n_lines, gw.first_bad);
-                                if (gw.first_bad < n_lines) hdr_err = gw.err;
+                                n_hdr = gw.n_c - 1u;
+                                if (gw.bad) {
+                                    bool no_sep = false;
+                                    n_hdr = bm_offender(bm, s0, gw, &no_sep);
+                                    hdr_err = no_sep ? SHL_E_HDR_NO_SEP : SHL_E_HDR_MULTI_SEP;
+                                }
                             } else if (sc.bad) n_hdr = count_lines(cr, sp, sc, &hdr_err, &s_skip);
                             else { n_hdr = sc.n_c - 1u; s_skip = sc.s_skip; }
                         }
@@ -665,44 +719,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
                 WellKnown w2; uint32_t n2 = 0;
                 w2.n_te = w2.n_cl = 0; w2.te_vs = w2.te_ve = w2.cl_vs = w2.cl_ve = 0;
                 headers_scalar(m, h0, T + 4, out, 1, nh, &n2, &w2);
-            } else {
-                // four lines per round: all eight byte peeks are in flight before the first is needed
-                int ls = h0;
-                const uint16_t* spp = coal ? &s_sp[warp][gw.js0] : sp + s_skip * 32;   // line k's ": " is at spp[k * lstride] - lsub
-                constexpr int kB = SHL_OPT_BATCH;
-                for (uint32_t k0 = 0; k0 < nh; k0 += kB) {
-                    int sepv[kB], endv[kB];
-                    uint32_t c0v[kB], c1v[kB];
-#pragma unroll
-                    for (int j = 0; j < kB; j++) {
-                        sepv[j] = endv[j] = 0; c0v[j] = c1v[j] = 'x';
-                        if (k0 + j < nh) {
-                            sepv[j] = (int)spp[(k0 + j) * lstride] - lsub; endv[j] = (int)crp[(k0 + j + 1) * lstride] - lsub;
-#ifndef SHL_EXP_NOPEEK
-                            if (sepv[j] + 2 < endv[j]) { c0v[j] = ldb(m + sepv[j] + 2); c1v[j] = ldb(m + endv[j] - 1); }
-#endif
-                        }
-                    }
-#pragma unroll
-                    for (int j = 0; j < kB; j++) {
-                        if (k0 + j < nh) {
-                            const int sep = sepv[j], end = endv[j];
-                            int vs = sep + 2, ve = end;
-                            if (is_ws(c0v[j]) || is_ws(c1v[j])) {
-                                while (vs < ve && is_ws(ldb(m + vs))) vs++;
-                                while (ve > vs && is_ws(ldb(m + ve - 1))) ve--;
-                            }
-                            const int klen = sep - ls;
-                            const uint32_t lo = (uint32_t)ls | ((uint32_t)klen << 16), hi = (uint32_t)vs | ((uint32_t)(ve - vs) << 16);
-                            *reinterpret_cast<uint2*>(out + k0 + j) = make_uint2(lo, hi);
-                            const uint32_t k0c = (klen == 14 || klen == 17) ? (ldb(m + ls) | 32u) : 0u;   // first letter screens the literal compare
-                            if (klen == 14 && k0c == 'c') { if (span_eq_lower(m, ls, sep, "content-length")) { if (!wk.n_cl) { wk.cl_vs = vs; wk.cl_ve = ve; } wk.n_cl++; } }
-                            else if (klen == 17 && k0c == 't') { if (span_eq_lower(m, ls, sep, "transfer-encoding")) { if (!wk.n_te) { wk.te_vs = vs; wk.te_ve = ve; } wk.n_te++; } }
-                            ls = end + 2;
-                        }
-                    }
-                }
-            }
+            } else if (coal) emit_records_bm(m, bm, gw.q_idx, (int)s0 + 1, h0, nh, out, wk);
+            else emit_records_lists(m, cr, sp + s_skip * 32, h0, nh, out, wk);
             r.n_headers = nh;
             if (hdr_err) r.status |= hdr_err;
             else finalize_headers(m, L, T + 4, get_or_head, wk, r.status, r.content_len);
@@ -726,17 +744,24 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
         if (kPlace && have) {
             const bool routable = (r.status & SHL_F_MESSAGE_COMPLETE) && (r.status & SHL_F_IS_REQUEST) &&
                                   (r.status & SHL_F_FIRST_LINE_DONE) && (r.status & 0xffu) == SHL_S_OK;
-            uint32_t h[4] = {0u, 0u, 0u, 0u}, node = 0xffffffffu;
+            uint32_t node = 0xffffffffu;
             if (routable) {
-                md5_key(m + r.sp1 + 1u, r.sp2 - r.sp1 - 1u, h);
-                node = ring_lookup(a.ring_values, a.ring_nodes, SHL_OPT_RINGDIR ? a.ring_dir : nullptr, a.n_points, a.n_hosts, h[0]);
+                if (!hashed) {
+                    uint32_t hh[4];
+                    md5_key(m + r.sp1 + 1u, r.sp2 - r.sp1 - 1u, hh);
+                    if (a.place.md5) reinterpret_cast<uint4*>(a.place.md5)[mine] = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+                    hash0 = hh[0];
+                }
+                node = ring_lookup(a.ring_values, a.ring_nodes, SHL_OPT_RINGDIR ? a.ring_dir : nullptr, a.n_points, a.n_hosts, hash0);
                 if (a.place.hist) {
                     if (smem_hist) atomicAdd(&s_hist[node], 1u);
                     else atomicAdd(reinterpret_cast<unsigned long long*>(a.place.hist) + node, 1ull);
                 }
+            } else {
+                hash0 = 0u;
+                if (a.place.md5) reinterpret_cast<uint4*>(a.place.md5)[mine] = make_uint4(0u, 0u, 0u, 0u);
             }
-            if (a.place.md5) reinterpret_cast<uint4*>(a.place.md5)[mine] = make_uint4(h[0], h[1], h[2], h[3]);
-            if (a.place.hash) a.place.hash[mine] = h[0];
+            if (a.place.hash) a.place.hash[mine] = hash0;
             if (a.place.node) a.place.node[mine] = node;
         }
     }

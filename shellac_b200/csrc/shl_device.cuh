@@ -34,6 +34,14 @@ __device__ __forceinline__ uint32_t ld32u(const uint8_t* p) {
     return __funnelshift_r(lo, hi, sh);
 }
 
+// unaligned little-endian 64-bit load (may touch up to 7 bytes past p+8, inside the arena padding)
+__device__ __forceinline__ uint64_t ld64u(const uint8_t* p) {
+    const uint32_t* a = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(p) & ~(uintptr_t)3);
+    const int sh = (int)(reinterpret_cast<uintptr_t>(p) & 3) * 8;
+    const uint32_t w0 = __ldg(a), w1 = __ldg(a + 1), w2 = sh ? __ldg(a + 2) : 0u;
+    return (uint64_t)__funnelshift_r(w0, w1, sh) | ((uint64_t)__funnelshift_r(w1, w2, sh) << 32);
+}
+
 // ASCII lower() of four packed bytes (bytes >= 0x80 are left alone, like Python 2's str.lower in the C locale)
 __device__ __forceinline__ uint32_t lower4(uint32_t x) {
     const uint32_t t = x & 0x7f7f7f7fu;
@@ -176,8 +184,14 @@ __device__ __forceinline__ void md5_block(uint32_t h[4], const uint32_t w[16]) {
     h[0] += a; h[1] += b; h[2] += c; h[3] += d;
 }
 
-// digest of key[0:n) into h[4] (little-endian words == digest bytes 0..15)
-__device__ __forceinline__ void md5_key(const uint8_t* key, uint32_t n, uint32_t h[4]) {
+// 0x80 in some byte <=> x holds a zero byte (exact as a yes / no answer)
+__device__ __forceinline__ uint32_t has_zero_byte(uint32_t x) { return (x - 0x01010101u) & ~x & 0x80808080u; }
+
+// digest of key[0:n) into h[4] (little-endian words == digest bytes 0..15).  kSpaces: also report
+// whether the key holds a ' ' (the route kernel takes the URL for granted between the first space
+// of the line and " HTTP/1.x"; a space inside it means split(' ', 2) cut elsewhere, HttpParser.py:307).
+template <bool kSpaces>
+__device__ __forceinline__ uint32_t md5_key_t(const uint8_t* key, uint32_t n, uint32_t h[4]) {
     h[0] = 0x67452301u; h[1] = 0xefcdab89u; h[2] = 0x98badcfeu; h[3] = 0x10325476u;
     const uint32_t* ap = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(key) & ~(uintptr_t)3);
     const uint32_t o = (uint32_t)(reinterpret_cast<uintptr_t>(key) & 3);
@@ -188,6 +202,7 @@ __device__ __forceinline__ void md5_key(const uint8_t* key, uint32_t n, uint32_t
     // wn, the word with the 0x80 pad at wn, zero above.
     const uint32_t nw = (n + o + 3u) >> 2, wn = n >> 2;
     const uint32_t r8 = (n & 3u) * 8u, km = (1u << r8) - 1u, pd = 0x80u << r8;
+    uint32_t spaces = 0u;
     uint32_t lo = (n > 0u) ? __ldg(ap) : 0u;
     for (uint32_t blk = 0; blk < nblk; blk++) {
         uint32_t w[16];
@@ -197,12 +212,31 @@ __device__ __forceinline__ void md5_key(const uint8_t* key, uint32_t n, uint32_t
             const uint32_t hi = (gi + 1u < nw) ? __ldg(ap + gi + 1u) : 0u;
             uint32_t x = __funnelshift_r(lo, hi, sh);
             lo = hi;
-            x = gi < wn ? x : (gi == wn ? ((x & km) | pd) : 0u);
+            x = gi < wn ? x : (gi == wn ? (x & km) : 0u);
+            if (kSpaces) spaces |= has_zero_byte(x ^ 0x20202020u);
+            if (gi == wn) x |= pd;
             if (blk == nblk - 1u) { if (i == 14) x = n << 3; if (i == 15) x = n >> 29; }
             w[i] = x;
         }
         md5_block(h, w);
     }
+    return spaces;
+}
+__device__ __forceinline__ void md5_key(const uint8_t* key, uint32_t n, uint32_t h[4]) { md5_key_t<false>(key, n, h); }
+
+// does p[0:n) hold a ' '?  (the same question without the digest, for the parse-only kernel)
+__device__ __forceinline__ bool span_has_space(const uint8_t* p, uint32_t n) {
+    const uint32_t* ap = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(p) & ~(uintptr_t)3);
+    const uint32_t o = (uint32_t)(reinterpret_cast<uintptr_t>(p) & 3);
+    const uint32_t nw = (n + o + 3u) >> 2;
+    uint32_t spaces = 0u;
+    for (uint32_t j = 0; j < nw; j++) {
+        uint32_t x = __ldg(ap + j);
+        if (j == 0u) x &= 0xffffffffu << (8u * o);
+        if (j == nw - 1u) { const uint32_t e = (n + o) & 3u; if (e) x &= 0xffffffffu >> (8u * (4u - e)); }
+        spaces |= has_zero_byte(x ^ 0x20202020u);
+    }
+    return n != 0u && spaces != 0u;
 }
 
 // lower_bound over the sorted continuum + wrap (libmemcached hash.c dispatch_host).

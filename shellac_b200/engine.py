@@ -185,6 +185,44 @@ class Engine(object):
         self.sync()
         return hl[:n], sz[:n], ok[:n]
 
+    # -- counters across GPUs (shl_stats_* / shl_comm_*: the library owns the NCCL communicator) --
+    def comm_init(self, comm_id, rank, world):
+        """Join the job's communicator: `comm_id` is the 128 bytes rank 0 got from comm_unique_id()."""
+        buf = (C.c_uint8 * N.COMM_ID_BYTES).from_buffer_copy(bytes(comm_id))
+        _check(self.lib, self.ctx, self.lib.shl_comm_init(self.ctx, buf, int(rank), int(world)), 'shl_comm_init')
+
+    def comm_unique_id(self):
+        buf = (C.c_uint8 * N.COMM_ID_BYTES)()
+        _check(self.lib, self.ctx, self.lib.shl_comm_unique_id(buf, N.COMM_ID_BYTES), 'shl_comm_unique_id')
+        return bytes(buf)
+
+    def stats_dev(self):
+        """Device address of the CURRENT counters buffer (changes with every stats_allreduce)."""
+        return self.lib.shl_stats_dev(self.ctx)
+
+    def stats_allreduce(self):
+        _check(self.lib, self.ctx, self.lib.shl_stats_allreduce(self.ctx), 'shl_stats_allreduce')
+
+    def stats_join(self):
+        _check(self.lib, self.ctx, self.lib.shl_stats_join(self.ctx), 'shl_stats_join')
+
+    def stats_fetch(self):
+        """[placement histogram n_hosts | outcome counts 64] of the most recent stats_allreduce."""
+        n = int(self.lib.shl_stats_len(self.ctx))
+        out = np.zeros(n, np.uint64)
+        _check(self.lib, self.ctx, self.lib.shl_stats_fetch(self.ctx, out.ctypes.data, n), 'shl_stats_fetch')
+        return out
+
+    def allreduce_u64(self, values, op='sum'):
+        """Small blocking all-reduce over the job's ranks (after draining this engine's streams)."""
+        v = np.ascontiguousarray(values, dtype=np.uint64).copy()
+        rc = self.lib.shl_comm_allreduce_u64(self.ctx, v.ctypes.data, len(v), 1 if op == 'max' else 0)
+        _check(self.lib, self.ctx, rc, 'shl_comm_allreduce_u64')
+        return v
+
+    def barrier(self):
+        self.allreduce_u64([1])
+
     def code_hist(self, reset=True):
         out = np.zeros(N.N_CODES, np.uint64)
         _check(self.lib, self.ctx, self.lib.shl_code_hist(self.ctx, out.ctypes.data, 1 if reset else 0), 'shl_code_hist')

@@ -1,6 +1,8 @@
 """The N>1 host logic on CPU: world_size-2 gloo run of the batch sharding and the histogram /
-outcome-counter all-reduce (the only collective the path has).  The per-rank placement comes from
-the oracle here; on GPUs bench.py feeds the same all-reduce from the kernel's device counters."""
+outcome-counter all-reduce (the only collective the path has), and the file rendezvous the ranks
+use to share the library's NCCL id.  The per-rank placement comes from the oracle here and the sum
+goes through gloo; on GPUs the library sums the kernel's device counters itself
+(shl_stats_allreduce, NCCL)."""
 import os
 import socket
 
@@ -42,8 +44,9 @@ def _worker(rank, world, port, n_total, q):
     klen = (po.sp2[:n] - po.sp1[:n] - 1).astype(np.uint32)
     pl = O.orc_place(ar, vals, nodes, 16, koff, klen)
     codes = np.bincount(po.status[:n] & 63, minlength=N.N_CODES)
+    import torch
     stats = D.pack_stats(pl.hist, codes)
-    D.allreduce_stats(stats)
+    dist.all_reduce(torch.from_numpy(stats), op=dist.ReduceOp.SUM)      # in place: the tensor shares the array
     if rank == 0:
         q.put(stats.tolist())
     dist.barrier()
@@ -91,3 +94,41 @@ def test_two_rank_gloo_allreduce_equals_single_rank():
                      (po.sp2[:n_total] - po.sp1[:n_total] - 1).astype(np.uint32))
     assert got[:16] == pl.hist.tolist() and sum(got[:16]) == n_total
     assert got[16 + N.S_OK] == n_total
+
+
+class _StubEngine(object):
+    """Stands in for Engine in the rendezvous test: records what join_job hands to the library."""
+
+    def __init__(self, q, bar):
+        self.q, self.bar = q, bar
+
+    def comm_unique_id(self):
+        return bytes(range(128))
+
+    def comm_init(self, cid, rank, world):
+        self.q.put((rank, world, bytes(cid)))
+
+    def barrier(self):
+        self.bar.wait(60)        # (ncclCommInitRank and the library's barrier are collective: so is this stand-in)
+
+
+def _rdzv_worker(rank, world, port, ppid_dir, q, bar):
+    from shellac_b200 import dist as D
+    os.environ.update({'RANK': str(rank), 'LOCAL_RANK': str(rank), 'WORLD_SIZE': str(world), 'MASTER_PORT': str(port),
+                       'SHL_RDZV_DIR': ppid_dir})
+    assert D.join_job(_StubEngine(q, bar)) == world
+
+
+def test_two_ranks_share_the_communicator_id(tmp_path):
+    import torch.multiprocessing as mp
+    ctx = mp.get_context('spawn')
+    q, bar = ctx.Queue(), ctx.Barrier(2)
+    ps = [ctx.Process(target=_rdzv_worker, args=(r, 2, 29999, str(tmp_path), q, bar)) for r in (1, 0)]   # rank 1 first: it has to wait
+    for p in ps:
+        p.start()
+    got = sorted(q.get(timeout=120) for _ in range(2))
+    for p in ps:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert [g[:2] for g in got] == [(0, 2), (1, 2)] and got[0][2] == got[1][2] == bytes(range(128))
+    assert not [f for f in os.listdir(str(tmp_path)) if f.endswith('.id')]        # rank 0 cleans up
