@@ -3,7 +3,7 @@
 
 The reference's hot path is two pure-Python files.  Where /root/reference is mounted (the build
 container; never the GPU box) this compiles them, UNMODIFIED and from where they lie, to CPython
-bytecode: oracle/_ref/HttpParser.pyc and StreamBuf.pyc.  Bytecode is the reference's "binary" for
+bytecode: oracle/_ref/HttpParser.bc and StreamBuf.bc (.pyc content; the extension keeps file-syncing tools that skip *.pyc from dropping them).  Bytecode is the reference's "binary" for
 this interpreter: oracle/_ref/ is git-ignored (no reference source enters the repository) but is
 not gpurun-ignored, so it travels to the GPU box like the built .so files do, and
 `bench.py --impl reference` can then time the reference itself (kind "reference") instead of the
@@ -41,7 +41,7 @@ def build_ref():
     done = []
     for name in FILES:
         src = os.path.join(REF_DIR, name + '.py')
-        dst = os.path.join(OUT, name + '.pyc')
+        dst = os.path.join(OUT, name + '.bc')
         if not os.path.exists(dst) or os.path.getmtime(dst) < os.path.getmtime(src):
             py_compile.compile(src, cfile=dst, doraise=True)
         done.append(dst)

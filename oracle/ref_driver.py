@@ -1,7 +1,7 @@
 """oracle/ref_driver.py — TEST / BENCH INFRASTRUCTURE: the reference's CPU path, as bench.py times it.
 
 `load_reference()` imports the UNMODIFIED reference parser from the bytecode oracle/build_ref.py
-made (oracle/_ref/HttpParser.pyc), behind the same three-line `cStringIO` shim SURVEY.md section 8c
+made (oracle/_ref/HttpParser.bc), behind the same three-line `cStringIO` shim SURVEY.md section 8c
 describes (the reference is Python 2; under CPython 3 it runs on `str`, one char per byte).  When
 oracle/_ref is absent the CPython port (oracle/py_port.py, pinned to the same golden vectors) stands in.
 
@@ -28,8 +28,9 @@ REF = os.path.join(HERE, '_ref')
 
 def load_reference():
     """(HttpParser class, 'reference') from oracle/_ref, or (None, 'port')."""
-    pyc = os.path.join(REF, 'HttpParser.pyc')
+    pyc = os.path.join(REF, 'HttpParser.bc')
     if not os.path.exists(pyc):
+        print('oracle/_ref/HttpParser.bc absent: the CPython port stands in', file=sys.stderr)
         return None, 'port'
     if 'cStringIO' not in sys.modules:
         m = types.ModuleType('cStringIO')
@@ -41,7 +42,8 @@ def load_reference():
         mod = importlib.util.module_from_spec(spec)
         loader.exec_module(mod)
         return mod.HttpParser, 'reference'
-    except Exception:       # noqa: BLE001 - bytecode of another interpreter version
+    except Exception as e:  # noqa: BLE001 - bytecode of another interpreter version
+        print('oracle/_ref present but not loadable (%r): the CPython port stands in' % (e,), file=sys.stderr)
         return None, 'port'
 
 

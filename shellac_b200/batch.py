@@ -226,11 +226,11 @@ class MessageView(object):
     def header_items(self):
         """(lower(key), stripped value) in arrival order (HttpParser.py:327-330)."""
         b, n = int(self.p.hdr_base[self.i]), int(self.p.n_headers[self.i])
-        out = []
-        for r in self.p.hdr[b:b + n]:
-            ko, kl, vo, vl = int(r['key_off']), int(r['key_len']), int(r['val_off']), int(r['val_len'])
-            out.append((self._lower(self.m[ko:ko + kl]), self._s(vo, vo + vl)))
-        return out
+        m = self.m
+        recs = np.ascontiguousarray(self.p.hdr[b:b + n]).view(np.uint16).reshape(-1, 4).tolist()     # one conversion per message
+        if not self.text:                 # bytes.lower(): ASCII only, like py2 str.lower()
+            return [(m[ko:ko + kl].lower(), m[vo:vo + vl]) for ko, kl, vo, vl in recs]
+        return [(m[ko:ko + kl].lower().decode('latin-1'), m[vo:vo + vl].decode('latin-1')) for ko, kl, vo, vl in recs]
 
     def _lower(self, k):
         k = k.lower()                     # bytes.lower(): ASCII only, like py2 str.lower()
@@ -238,6 +238,9 @@ class MessageView(object):
 
     def headers(self):
         """dict with duplicate keys folded into lists in arrival order (HttpParser.py:331-337)."""
+        d = getattr(self, '_hd', None)
+        if d is not None and self._hd_text == self.text:
+            return d
         d = {}
         for k, v in self.header_items():
             if k in d:
@@ -247,6 +250,7 @@ class MessageView(object):
                     d[k] = [d[k], v]
             else:
                 d[k] = v
+        self._hd, self._hd_text = d, self.text
         return d
 
     def headers_complete(self):

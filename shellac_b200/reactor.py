@@ -14,16 +14,26 @@ peeled off in further rounds of the same tick (Server.py:320 `while len(data) !=
 `router` is anything with `route(messages) -> (parse_out, place_out, frame_out_or_None)`;
 `EngineRouter` below is the real one.  There is no CPU path in this package.
 """
+import numpy as np
+
 from . import _native as N
 from .batch import MessageView
 
 
 class Routed(object):
-    """One completed request: what Server._read_requests has in hand at Server.py:325-335."""
-    __slots__ = ('fd', 'view', 'key', 'node', 'error', 'raw')
+    """One completed request: what Server._read_requests has in hand at Server.py:325-335.
+    `.view` (the parser-shaped MessageView of the request) is built when it is first asked for."""
+    __slots__ = ('fd', '_view', '_src', 'key', 'node', 'error', 'raw')
 
-    def __init__(self, fd, view, key, node, error, raw):
-        self.fd, self.view, self.key, self.node, self.error, self.raw = fd, view, key, node, error, raw
+    def __init__(self, fd, view, key, node, error, raw, src=None):
+        self.fd, self._view, self._src, self.key, self.node, self.error, self.raw = fd, view, src, key, node, error, raw
+
+    @property
+    def view(self):
+        if self._view is None and self._src is not None:
+            msg, pout, i, fout = self._src
+            self._view = MessageView(msg, pout, i, fout)
+        return self._view
 
 
 class EngineRouter(object):
@@ -64,19 +74,13 @@ class _Bag(object):
 
 
 def _detach_parse(p, n):
-    b = _Bag()
-    for name, _ in N.PARSE_FIELDS:
-        setattr(b, name, getattr(p, name)[:n].copy())
-    b.hdr = p.hdr[:int(p.hdr_used[0])].copy()
-    return b
+    from .server.HttpParser import detach_parse
+    return detach_parse(p, n)
 
 
 def _detach_frame(f, n):
-    b = _Bag()
-    for name, _ in N.FRAME_FIELDS:
-        setattr(b, name, getattr(f, name)[:n].copy())
-    b.chunk = f.chunk[:int(f.chunk_used[0])].copy()
-    return b
+    from .server.HttpParser import detach_frame
+    return detach_frame(f, n)
 
 
 def _detach_place(q, n):
@@ -114,7 +118,34 @@ class ReactorShim(object):
             msgs = [bytes(self.pending[fd]) for fd in live]
             pout, qout, fout = self.router.route(msgs)
             late_keys, late_items, again = [], [], []
+            # Per request only status, bytes consumed, URL span and node are needed: they are worked
+            # out for the whole round with array arithmetic.  Whole, un-chunked requests (the bulk
+            # of a tick) never get a Python parser object unless the caller asks for `.view`.
+            n = len(live)
+            st = np.asarray(pout.status[:n])
+            code = st & 0xff
+            plain = ((st & (N.F_MESSAGE_COMPLETE | N.F_IS_REQUEST | N.F_FIRST_LINE_DONE)) ==
+                     (N.F_MESSAGE_COMPLETE | N.F_IS_REQUEST | N.F_FIRST_LINE_DONE)) & (code == N.S_OK) & \
+                    ((st & (N.F_CHUNKED | N.F_CLEN_WIDE)) == 0)
+            body = np.where((st & N.F_ON_BODY) == 0, np.asarray(pout.content_len[:n]), 0)
+            used_v = (np.asarray(pout.first_line_len[:n]).astype(np.int64) + pout.headers_len[:n] + body).tolist()
+            sp1_v, sp2_v = np.asarray(pout.sp1[:n]).tolist(), np.asarray(pout.sp2[:n]).tolist()
+            node_v = np.asarray(qout.node[:n]).tolist()
+            waiting = ((code == N.S_INCOMPLETE_LINE) | (code == N.S_INCOMPLETE_HEADERS) | (code == N.S_EMPTY) |
+                       ((code == N.S_INCOMPLETE_BODY) & ((st & N.F_CHUNKED) == 0))).tolist()
+            plain = plain.tolist()
+            pending = self.pending
             for i, fd in enumerate(live):
+                if plain[i]:
+                    msg, used = msgs[i], used_v[i]
+                    buf = pending[fd]
+                    del buf[:used]
+                    done.append(Routed(fd, None, msg[sp1_v[i] + 1:sp2_v[i]], node_v[i], None, msg[:used], (msg, pout, i, fout)))
+                    if buf:
+                        again.append(fd)
+                    continue
+                if waiting[i]:
+                    continue                                   # wait for more bytes (next tick)
                 v = MessageView(msgs[i], pout, i, fout)
                 exc = v.exception()
                 if exc is not None:
@@ -122,7 +153,7 @@ class ReactorShim(object):
                     self.pending[fd] = bytearray()
                     continue
                 if not v.message_complete():
-                    continue                                   # wait for more bytes (next tick)
+                    continue
                 used = v.consumed()
                 raw = msgs[i][:used]
                 del self.pending[fd][:used]

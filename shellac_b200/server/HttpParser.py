@@ -40,39 +40,50 @@ class DeviceBackend(object):
         self._pb = PinnedBatch(engine)
         self._ch = (engine.pinned(1, np.int32), engine.pinned(1, np.uint64), engine.pinned(1, np.uint8))
 
-    def views(self, bufs, frame=False):
-        """MessageView per buffer (bytes).  The views own copies of their rows; the pinned staging
-        area is kept between calls and only grows."""
+    def batch(self, bufs, frame=False):
+        """One device call for a list of buffers (bytes): (parse rows, frame rows or None), detached
+        from the pinned staging area, which is kept between calls and only grows."""
         eng, pb = self.eng, self._pb
         ar = pb.pack(bufs)
         po = eng.parse(ar, out=pb.pout)
-        fo = eng.frame(ar, po, reuse_arena=True, out=pb.fout, chunk_cap=pb.fout.chunk_cap) if frame else None
-        return [MessageView(bufs[i], _Row(po, i), 0, _FrameRow(fo, i) if fo is not None else None)
-                for i in range(len(bufs))]
+        fo = None
+        if frame and len(bufs) and ((po.status[:ar.n] & N.F_CHUNKED) != 0).any():
+            fo = eng.frame(ar, po, reuse_arena=True, out=pb.fout, chunk_cap=pb.fout.chunk_cap)
+        return detach_parse(po, ar.n), (detach_frame(fo, ar.n) if fo is not None else None)
+
+    def views(self, bufs, frame=False):
+        """MessageView per buffer (bytes)."""
+        po, fo = self.batch(bufs, frame)
+        return [MessageView(bufs[i], po, i, fo) for i in range(len(bufs))]
 
     def chunk_header(self, buf):
         hl, sz, ok = self.eng.chunk_header(self._pb.pack([buf]), out=self._ch)
         return int(hl[0]), int(sz[0]), bool(ok[0])
 
 
-class _Row(object):
-    """One message's slice of a ParseOut, detached from the pinned arrays."""
-
-    def __init__(self, po, i):
-        for name, _ in N.PARSE_FIELDS:
-            setattr(self, name, [getattr(po, name)[i].item()])
-        b, n = int(po.hdr_base[i]), int(po.n_headers[i])
-        self.hdr = po.hdr[b:b + n].copy()
-        self.hdr_base = [0]
+class _Rows(object):
+    pass
 
 
-class _FrameRow(object):
-    def __init__(self, fo, i):
-        for name, _ in N.FRAME_FIELDS:
-            setattr(self, name, [getattr(fo, name)[i].item()])
-        b, n = int(fo.chunk_base[i]), int(fo.n_chunks[i])
-        self.chunk = fo.chunk[b:b + n].copy()
-        self.chunk_base = [0]
+def detach_parse(p, n):
+    """Copies of the first n rows of a ParseOut and of the header records they point at.  (On the
+    chunked large-batch path each chunk's records start at its own slice of the arena, so the
+    records in use end at max(hdr_base + n_headers), not at the sum of the counts.)"""
+    r = _Rows()
+    for name, _ in N.PARSE_FIELDS:
+        setattr(r, name, getattr(p, name)[:n].copy())
+    end = int((r.hdr_base.astype(np.int64) + r.n_headers).max()) if n else 0
+    r.hdr = p.hdr[:end].copy()
+    return r
+
+
+def detach_frame(f, n):
+    r = _Rows()
+    for name, _ in N.FRAME_FIELDS:
+        setattr(r, name, getattr(f, name)[:n].copy())
+    end = int((r.chunk_base.astype(np.int64) + r.n_chunks).max()) if n else 0
+    r.chunk = f.chunk[:end].copy()
+    return r
 
 
 _default_backend = None
@@ -357,26 +368,57 @@ class HttpParser(object):
     def parse_many(cls, messages, backend=None):
         """One device call for a list of whole messages; returns a parser object per message in
         the state the reference object is in after being driven over that message.  A message
-        whose parse raised in the reference carries the exception in `.error` instead."""
+        whose parse raised in the reference carries the exception in `.error` instead.  The
+        objects are cheap: each turns its row of the batch result into Python values on first use."""
         be = backend or default_backend()
         text = [isinstance(m, str) for m in messages]
-        bufs = [m.encode('latin-1') if isinstance(m, str) else bytes(m) for m in messages]
-        out = []
-        for v, is_text in zip(be.views(bufs, frame=True), text):
-            v.text = is_text
-            p = cls(backend=be)
-            p._text = is_text
-            p._is_request, p._version = v.is_request(), v.version()
-            un = (lambda x: x.encode('latin-1') if isinstance(x, str) else x)
-            p._method, p._url, p._message, p._status = un(v.method()), un(v.url()), un(v.message()), v.status()
-            p._headers = v.headers()
-            p._headers_complete, p._message_complete = v.headers_complete(), v.message_complete()
-            p._chunked, p._on_body = v.chunked(), v.on_body()
-            p._on_first_line = not (v.st & N.F_FIRST_LINE_DONE)
-            p._on_headers = bool(v.st & N.F_FIRST_LINE_DONE) and not p._headers_complete
-            p._body = v.body()
-            p.calls = v.calls()
-            exc = v.exception()
-            p.error = exc() if exc else None
-            out.append(p)
-        return out
+        any_text = any(text)
+        bufs = [m.encode('latin-1') if isinstance(m, str) else bytes(m) for m in messages] if any_text else \
+               [m if type(m) is bytes else bytes(m) for m in messages]
+        po, fo = be.batch(bufs, frame=True) if hasattr(be, 'batch') else _rows_of_views(be, bufs)
+        mk = _LazyParser
+        if not any_text:
+            return [mk(be, po, fo, bufs[i], i, False) for i in range(len(bufs))]
+        return [mk(be, po, fo, bufs[i], i, text[i]) for i in range(len(bufs))]
+
+
+def _rows_of_views(be, bufs):
+    """Backends that only offer views() (the oracle-backed one of the CPU tests)."""
+    vs = be.views(bufs, frame=True)
+    return (vs[0].p, vs[0].f) if vs else (None, None)
+
+
+class _LazyParser(HttpParser):
+    """A parser object of parse_many: row `i` of a batch result.  Nothing is converted until an
+    attribute is asked for; then the whole object is filled in once (so every getter of the
+    reference's surface, and the incremental state flags, behave as on a driven parser)."""
+
+    def __init__(self, backend, po, fo, buf, i, text):   # noqa: super().__init__ is what _fill replaces
+        d = self.__dict__
+        d['_backend'], d['_lazy'] = backend, (po, fo, buf, i, text)
+
+    def __getattr__(self, name):
+        lazy = self.__dict__.get('_lazy')
+        if lazy is None or name.startswith('__'):
+            raise AttributeError(name)
+        self._fill(lazy)
+        return object.__getattribute__(self, name)
+
+    def _fill(self, lazy):
+        po, fo, buf, i, is_text = lazy
+        self.__dict__['_lazy'] = None
+        HttpParser.__init__(self, backend=self._backend)
+        v = MessageView(buf, po, i, fo, text=is_text)
+        self._text = is_text
+        self._is_request, self._version = v.is_request(), v.version()
+        un = (lambda x: x.encode('latin-1') if isinstance(x, str) else x)
+        self._method, self._url, self._message, self._status = un(v.method()), un(v.url()), un(v.message()), v.status()
+        self._headers = v.headers()
+        self._headers_complete, self._message_complete = v.headers_complete(), v.message_complete()
+        self._chunked, self._on_body = v.chunked(), v.on_body()
+        self._on_first_line = not (v.st & N.F_FIRST_LINE_DONE)
+        self._on_headers = bool(v.st & N.F_FIRST_LINE_DONE) and not self._headers_complete
+        self._body = v.body()
+        self.calls = v.calls()
+        exc = v.exception()
+        self.error = exc() if exc else None

@@ -6,6 +6,11 @@ from tests import oracle_lib as O
 
 
 class OracleBackend(object):
+    def batch(self, bufs, frame=False):
+        ar = Arena.pack(bufs)
+        po = O.orc_parse(ar)
+        return po, (O.orc_frame(ar, po) if frame else None)
+
     def views(self, bufs, frame=False):
         ar = Arena.pack(bufs)
         po = O.orc_parse(ar)
