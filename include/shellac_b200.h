@@ -71,6 +71,11 @@ enum {
 #define SHL_F_STATUS_WIDE        (1u << 15)  /* int(status) valid but does not fit status_code: host converts the span */
 #define SHL_F_CLEN_WIDE          (1u << 16)  /* int(content-length) valid but beyond int64: host converts the span     */
 #define SHL_F_FIRST_LINE_DONE    (1u << 17)  /* _parse_first_line returned (fields below are valid)                   */
+#define SHL_F_KEY_TOO_LONG       (1u << 18)  /* request whose cache key (the URL, Server.py:327) is longer than
+                                              * SHL_MAX_KEY_LEN: pylibmc raises ValueError before hashing, at
+                                              * Server.py:335; such a request is parsed but NOT placed
+                                              * (node = 0xffffffff, digest zero, not counted in the histogram)        */
+#define SHL_MAX_KEY_LEN          250         /* MEMCACHED_MAX_KEY - 1 (libmemcached constants.h; restated)            */
 
 /* One header line, offsets relative to the first byte of the message.
  * key   = line[:sep]            (NOT stripped; the reference lower()s it, HttpParser.py:330)
@@ -107,6 +112,14 @@ typedef struct shl_parse_out {
     shl_hdr_span* hdr;         /* record arena, `hdr_cap` entries                                  */
     uint64_t  hdr_cap;
     uint64_t* hdr_used;        /* one element: records written                                     */
+    /* Optional (all four NULL / 0 = not wanted): the header NAMES lower-cased as the reference stores
+     * them (key.lower(), HttpParser.py:330; ASCII only, like Python 2's str.lower()).  Message i's
+     * names lie back to back, in record order, from lkeys[lkey_base[i]]: name k starts
+     * sum(key_len[0..k-1]) bytes in and is key_len[k] long.                                        */
+    uint8_t*  lkeys;           /* byte arena, `lkeys_cap` bytes                                    */
+    uint64_t  lkeys_cap;
+    uint64_t* lkeys_used;      /* one element: bytes handed out                                    */
+    uint32_t* lkey_base;       /* [n]                                                              */
 } shl_parse_out;
 
 /* Chunked-body framing result (struct-of-arrays, n elements each). */

@@ -230,10 +230,21 @@ static void parse_one(const uint8_t* m, int64_t L, msg_rec* r, shl_hdr_span* hdr
 
 int orc_parse(const uint8_t* arena, const uint64_t* off, const uint32_t* len, uint64_t n,
               const shl_parse_out* out) {
-    uint64_t used = 0;
+    uint64_t used = 0, kused = 0;
     for (uint64_t i = 0; i < n; i++) {
         msg_rec r;
         parse_one(arena + off[i], (int64_t)len[i], &r, out->hdr + used, out->hdr_cap - used);
+        /* key = request.url() (Server.py:327); pylibmc refuses keys over 250 bytes before hashing (:335) */
+        if ((r.status & SHL_F_IS_REQUEST) && (r.status & SHL_F_FIRST_LINE_DONE) && r.sp2 - r.sp1 - 1 > SHL_MAX_KEY_LEN)
+            r.status |= SHL_F_KEY_TOO_LONG;
+        if (out->lkeys) {                                    /* key.lower(), HttpParser.py:330 */
+            out->lkey_base[i] = (uint32_t)kused;
+            for (uint32_t k = 0; k < r.n_headers; k++) {
+                const shl_hdr_span* h = out->hdr + used + k;
+                for (uint32_t j = 0; j < h->key_len && kused < out->lkeys_cap; j++)
+                    out->lkeys[kused++] = lower(arena[off[i] + h->key_off + j]);
+            }
+        }
         out->status[i] = r.status; out->first_line_len[i] = r.first_line_len;
         out->headers_len[i] = r.headers_len; out->sp1[i] = r.sp1; out->sp2[i] = r.sp2;
         out->fl_end[i] = r.fl_end; out->slash[i] = r.slash; out->status_code[i] = r.status_code;
@@ -242,6 +253,7 @@ int orc_parse(const uint8_t* arena, const uint64_t* off, const uint32_t* len, ui
         used += r.n_headers;
     }
     *out->hdr_used = used;
+    if (out->lkeys_used) *out->lkeys_used = kused;
     return 0;
 }
 

@@ -24,6 +24,8 @@ F_IS_REQUEST, F_HEADERS_COMPLETE, F_MESSAGE_COMPLETE = 1 << 8, 1 << 9, 1 << 10
 F_ON_BODY, F_CHUNKED = 1 << 11, 1 << 12
 F_VERSION_SHIFT = 13
 F_STATUS_WIDE, F_CLEN_WIDE, F_FIRST_LINE_DONE = 1 << 15, 1 << 16, 1 << 17
+F_KEY_TOO_LONG = 1 << 18
+MAX_KEY_LEN = 250
 FS_NOT_CHUNKED = 0xff
 RING_KETAMA, RING_KETAMA_WEIGHTED = 0, 1
 N_CODES = 64          # SHL_N_CODES: histogram length for per-outcome counts
@@ -53,7 +55,8 @@ class ParseOutStruct(C.Structure):
                 ('sp1', C.c_void_p), ('sp2', C.c_void_p), ('fl_end', C.c_void_p), ('slash', C.c_void_p),
                 ('status_code', C.c_void_p), ('n_headers', C.c_void_p), ('hdr_base', C.c_void_p),
                 ('content_len', C.c_void_p), ('hdr', C.c_void_p), ('hdr_cap', C.c_uint64),
-                ('hdr_used', C.c_void_p)]
+                ('hdr_used', C.c_void_p), ('lkeys', C.c_void_p), ('lkeys_cap', C.c_uint64),
+                ('lkeys_used', C.c_void_p), ('lkey_base', C.c_void_p)]
 
 
 class FrameOutStruct(C.Structure):

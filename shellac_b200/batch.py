@@ -67,12 +67,26 @@ class Arena(object):
 
 
 class ParseOut(object):
-    def __init__(self, n, hdr_cap, alloc=_np_alloc):
-        self.n, self.hdr_cap = int(n), int(hdr_cap)
+    def __init__(self, n, hdr_cap, alloc=_np_alloc, lkeys_cap=0):
+        """lkeys_cap > 0 also asks for the header names lower-cased on the device (key.lower(),
+        HttpParser.py:330): `lkeys` arena + `lkey_base[i]`, see include/shellac_b200.h."""
+        self.n, self.hdr_cap, self.lkeys_cap = int(n), int(hdr_cap), int(lkeys_cap)
         for name, dt in N.PARSE_FIELDS:
             setattr(self, name, alloc(n, dt))
         self.hdr = alloc(hdr_cap, N.HDR_DTYPE)
         self.hdr_used = alloc(1, np.uint64)
+        self.lkeys = self.lkeys_used = self.lkey_base = None
+        if lkeys_cap:
+            self.lkeys, self.lkeys_used, self.lkey_base = alloc(lkeys_cap, np.uint8), alloc(1, np.uint64), alloc(n, np.uint32)
+
+    def lower_keys(self, i):
+        """Message i's header names as the device lower-cased them, in record order."""
+        b, k = int(self.hdr_base[i]), int(self.n_headers[i])
+        p, out = int(self.lkey_base[i]), []
+        for kl in self.hdr['key_len'][b:b + k].tolist():
+            out.append(self.lkeys[p:p + kl].tobytes())
+            p += kl
+        return out
 
     def struct(self):
         """The C struct of this object's array addresses (built once: the arrays never move)."""
@@ -82,6 +96,9 @@ class ParseOut(object):
             for name, _ in N.PARSE_FIELDS:
                 setattr(s, name, getattr(self, name).ctypes.data)
             s.hdr, s.hdr_cap, s.hdr_used = self.hdr.ctypes.data, self.hdr_cap, self.hdr_used.ctypes.data
+            if self.lkeys is not None:
+                s.lkeys, s.lkeys_cap = self.lkeys.ctypes.data, self.lkeys_cap
+                s.lkeys_used, s.lkey_base = self.lkeys_used.ctypes.data, self.lkey_base.ctypes.data
             self._struct = s
         return s
 

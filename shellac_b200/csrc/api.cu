@@ -59,6 +59,7 @@ struct shl_ctx {
     ncclComm_t comm = nullptr; int comm_rank = 0, comm_world = 1;
     uint64_t* d_scratch = nullptr; uint64_t* h_scratch = nullptr;             // 64 words for shl_comm_allreduce_u64
     uint64_t cur_n = 0;                   // messages of the last *_batch parse (frame_batch checks it)
+    uint8_t* d_lkeys = nullptr; uint32_t* d_lkey_base = nullptr;   // lower-cased header names (lazy; d_counters[2] counts the bytes)
     int force_scalar = 0;
     int sm_count = 148, grid_waves = 16;
     uint64_t launches = 0;
@@ -306,6 +307,7 @@ void shl_ctx_destroy(shl_ctx* ctx) {
     for (auto& e : ctx->ev_stats_done) if (e) cudaEventDestroy(e);
     cudaFree(ctx->d_ring_values); cudaFree(ctx->d_ring_nodes); cudaFree(ctx->d_ring_dir); cudaFree(ctx->d_hist);
     cudaFree(ctx->d_body); cudaFree(ctx->d_body_off); cudaFree(ctx->d_body_len);
+    cudaFree(ctx->d_lkeys); cudaFree(ctx->d_lkey_base);
     cudaFree(ctx->d_gstart); cudaFree(ctx->d_gcursor); cudaFree(ctx->d_gorder);
     for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
     for (auto& st : ctx->pipe) if (st) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
@@ -760,10 +762,34 @@ static int route_pipelined(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_by
     return SHL_OK;
 }
 
+// The caller asked for the lower-cased header names: give the device parse block the arena for
+// them (allocated on first use: header names cannot outgrow the message bytes).
+static int with_lkeys(shl_ctx* ctx, const shl_parse_out* host, shl_parse_out* dev) {
+    *dev = ctx->dp;
+    if (!host->lkeys) return SHL_OK;
+    if (!host->lkeys_used || !host->lkey_base) return fail(ctx, SHL_ERR_ARG, "lkeys needs lkeys_used and lkey_base too");
+    if (!ctx->d_lkeys) { CU(dalloc(&ctx->d_lkeys, ctx->max_bytes + 64)); CU(dalloc(&ctx->d_lkey_base, ctx->max_msgs)); }
+    dev->lkeys = ctx->d_lkeys; dev->lkeys_cap = std::min<uint64_t>(ctx->max_bytes, host->lkeys_cap);
+    dev->lkeys_used = ctx->d_counters + 2; dev->lkey_base = ctx->d_lkey_base;
+    CU(cudaMemsetAsync(ctx->d_counters + 2, 0, 8, ctx->stream));
+    return SHL_OK;
+}
+static int lkeys_d2h(shl_ctx* ctx, const shl_parse_out* host, uint64_t n) {
+    if (!host->lkeys) return SHL_OK;
+    CU(cudaMemcpyAsync(host->lkey_base, ctx->d_lkey_base, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->h_counters + 2, ctx->d_counters + 2, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    const uint64_t used = ctx->h_counters[2];
+    *host->lkeys_used = used;
+    if (used > std::min<uint64_t>(ctx->max_bytes, host->lkeys_cap)) return fail(ctx, SHL_ERR_CAPACITY, "lower-cased key arena overflowed: raise lkeys_cap");
+    if (used) CU(cudaMemcpyAsync(host->lkeys, ctx->d_lkeys, used, cudaMemcpyDeviceToHost, ctx->stream));
+    return SHL_OK;
+}
+
 int shl_parse_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, const uint64_t* off, const uint32_t* len,
                     uint64_t n, const shl_parse_out* out) {
     if (!out) return fail(ctx, SHL_ERR_ARG, "out is null");
-    if (ctx && off && len && n <= ctx->max_msgs && arena_bytes <= ctx->max_bytes) {
+    if (ctx && off && len && n <= ctx->max_msgs && arena_bytes <= ctx->max_bytes && !out->lkeys) {
         CU(cudaSetDevice(ctx->device));
         int rc = route_small(ctx, arena, arena_bytes, off, len, n, out, nullptr);
         if (rc <= 0) return rc;
@@ -773,15 +799,18 @@ int shl_parse_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, co
     if (int rc = stage_in(ctx, arena, arena_bytes, off, len, n, ctx->d_off, ctx->d_len)) return rc;
     CU(cudaMemsetAsync(ctx->d_counters, 0, 8, ctx->stream));
     ctx->cur_dp = ctx->dp; ctx->cur_n = n;
-    if (int rc = shl_parse_dev(ctx, ctx->d_arena, ctx->d_off, ctx->d_len, n, &ctx->dp)) return rc;
-    return parse_out_d2h(ctx, out, n);
+    shl_parse_out dp;
+    if (int rc = with_lkeys(ctx, out, &dp)) return rc;
+    if (int rc = shl_parse_dev(ctx, ctx->d_arena, ctx->d_off, ctx->d_len, n, &dp)) return rc;
+    if (int rc = parse_out_d2h(ctx, out, n)) return rc;
+    return lkeys_d2h(ctx, out, n);
 }
 
 int shl_route_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, const uint64_t* off, const uint32_t* len,
                     uint64_t n, const shl_parse_out* pout, const shl_place_out* qout) {
     if (!pout || !qout) return fail(ctx, SHL_ERR_ARG, "out is null");
     if (ctx && !ctx->d_ring_values) return fail(ctx, SHL_ERR_NO_RING, "shl_ring_build() has not been called");
-    if (ctx && off && len && n <= ctx->max_msgs && arena_bytes <= ctx->max_bytes) {
+    if (ctx && off && len && n <= ctx->max_msgs && arena_bytes <= ctx->max_bytes && !pout->lkeys) {
         CU(cudaSetDevice(ctx->device));
         int rc = route_small(ctx, arena, arena_bytes, off, len, n, pout, qout);
         if (rc <= 0) return rc;
@@ -795,8 +824,11 @@ int shl_route_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, co
     if (dq.hist) CU(cudaMemsetAsync(ctx->d_hist, 0, (size_t)ctx->n_hosts * 8, ctx->stream));
     ctx->cur_dp = ctx->dp; ctx->cur_n = n;
     ctx->cur_node = ctx->dq.node; ctx->cur_hist = dq.hist;
-    if (int rc = shl_route_dev(ctx, ctx->d_arena, ctx->d_off, ctx->d_len, n, &ctx->dp, &dq)) return rc;
+    shl_parse_out dp;
+    if (int rc = with_lkeys(ctx, pout, &dp)) return rc;
+    if (int rc = shl_route_dev(ctx, ctx->d_arena, ctx->d_off, ctx->d_len, n, &dp, &dq)) return rc;
     if (int rc = parse_out_d2h(ctx, pout, n)) return rc;
+    if (int rc = lkeys_d2h(ctx, pout, n)) return rc;
     return place_out_d2h(ctx, qout, n);
 }
 

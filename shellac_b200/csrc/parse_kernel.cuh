@@ -726,6 +726,33 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
             else finalize_headers(m, L, T + 4, get_or_head, wk, r.status, r.content_len);
         }
 
+        // ---- optional: the header names lower-cased (key.lower(), HttpParser.py:330), packed per message
+        if (a.out.lkeys != nullptr) {
+            const shl_hdr_span* recs = a.out.hdr + my_base;
+            uint32_t kb = 0;
+            for (uint32_t k = 0; k < r.n_headers; k++) kb += recs[k].key_len;
+            uint32_t kinc = kb;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(SHL_FULL, kinc, d); if (lane >= d) kinc += t; }
+            const uint32_t ktot = __shfl_sync(SHL_FULL, kinc, 31);
+            unsigned long long kbase = 0;
+            if (lane == 0 && ktot) kbase = atomicAdd(reinterpret_cast<unsigned long long*>(a.out.lkeys_used), (unsigned long long)ktot);
+            kbase = __shfl_sync(SHL_FULL, kbase, 0) + (kinc - kb);
+            if (have) {
+                a.out.lkey_base[mine] = (uint32_t)kbase;
+                if (kbase + kb <= a.out.lkeys_cap) {
+                    uint8_t* dst = a.out.lkeys + kbase;
+                    for (uint32_t k = 0; k < r.n_headers; k++) {
+                        const shl_hdr_span rec = recs[k];
+                        for (uint32_t j = 0; j < rec.key_len; j++) dst[j] = (uint8_t)lower(ldb(m + rec.key_off + j));
+                        dst += rec.key_len;
+                    }
+                } else r.status = (r.status & ~0xffu) | SHL_E_LIB_RECORDS_FULL;
+            }
+        }
+        if ((r.status & (SHL_F_IS_REQUEST | SHL_F_FIRST_LINE_DONE)) == (SHL_F_IS_REQUEST | SHL_F_FIRST_LINE_DONE) &&
+            r.sp2 - r.sp1 - 1u > (uint32_t)SHL_MAX_KEY_LEN) r.status |= SHL_F_KEY_TOO_LONG;      // pylibmc raises before hashing (Server.py:335)
+
         // ---- per-message fixed fields: lane j == message j, so these are coalesced SoA stores
         if (have) {
             a.out.status[mine] = r.status;
@@ -743,7 +770,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
         // ---- fused key + MD5 + ketama: the URL is the key, verbatim  (Server.py:325-335)
         if (kPlace && have) {
             const bool routable = (r.status & SHL_F_MESSAGE_COMPLETE) && (r.status & SHL_F_IS_REQUEST) &&
-                                  (r.status & SHL_F_FIRST_LINE_DONE) && (r.status & 0xffu) == SHL_S_OK;
+                                  (r.status & SHL_F_FIRST_LINE_DONE) && (r.status & 0xffu) == SHL_S_OK &&
+                                  !(r.status & SHL_F_KEY_TOO_LONG);
             uint32_t node = 0xffffffffu;
             if (routable) {
                 if (!hashed) {

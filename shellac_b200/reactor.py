@@ -126,7 +126,7 @@ class ReactorShim(object):
             code = st & 0xff
             plain = ((st & (N.F_MESSAGE_COMPLETE | N.F_IS_REQUEST | N.F_FIRST_LINE_DONE)) ==
                      (N.F_MESSAGE_COMPLETE | N.F_IS_REQUEST | N.F_FIRST_LINE_DONE)) & (code == N.S_OK) & \
-                    ((st & (N.F_CHUNKED | N.F_CLEN_WIDE)) == 0)
+                    ((st & (N.F_CHUNKED | N.F_CLEN_WIDE | N.F_KEY_TOO_LONG)) == 0)
             body = np.where((st & N.F_ON_BODY) == 0, np.asarray(pout.content_len[:n]), 0)
             used_v = (np.asarray(pout.first_line_len[:n]).astype(np.int64) + pout.headers_len[:n] + body).tolist()
             sp1_v, sp2_v = np.asarray(pout.sp1[:n]).tolist(), np.asarray(pout.sp2[:n]).tolist()
@@ -160,7 +160,9 @@ class ReactorShim(object):
                 key = v.url()
                 node = int(qout.node[i]) if key is not None else None
                 item = Routed(fd, v, key, node, None, raw)
-                if key is not None and node == 0xffffffff:     # completed by the chunk framer: place it now
+                if v.st & N.F_KEY_TOO_LONG:                    # pylibmc raises before hashing (Server.py:335)
+                    item.node, item.error = None, ValueError('key too long, max is %d' % N.MAX_KEY_LEN)
+                elif key is not None and node == 0xffffffff:   # completed by the chunk framer: place it now
                     late_keys.append(key)
                     late_items.append(item)
                 done.append(item)

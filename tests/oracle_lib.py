@@ -42,9 +42,10 @@ def oracle():
     return _orc
 
 
-def orc_parse(arena, hdr_cap=None):
+def orc_parse(arena, hdr_cap=None, lkeys=False):
     n = arena.n
-    out = ParseOut(n, hdr_cap if hdr_cap is not None else max(16, arena.nbytes // 4 + 16))
+    out = ParseOut(n, hdr_cap if hdr_cap is not None else max(16, arena.nbytes // 4 + 16),
+                   lkeys_cap=arena.nbytes + 16 if lkeys else 0)
     s = out.struct()
     oracle().orc_parse(arena.data.ctypes.data, arena.off.ctypes.data, arena.len.ctypes.data, n, C.byref(s))
     return out

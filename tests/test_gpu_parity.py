@@ -468,7 +468,8 @@ def test_route_fused_matches_parse_then_place(eng, golden):
     o = O.orc_parse(ar)
     assert_parse_equal(ar, pg, o, 'route parse fields')
     st = o.status[:n]
-    routable = ((st & N.F_MESSAGE_COMPLETE) != 0) & ((st & N.F_IS_REQUEST) != 0) & ((st & N.F_FIRST_LINE_DONE) != 0) & ((st & 0xff) == 0)
+    routable = ((st & N.F_MESSAGE_COMPLETE) != 0) & ((st & N.F_IS_REQUEST) != 0) & ((st & N.F_FIRST_LINE_DONE) != 0) & ((st & 0xff) == 0) & \
+               ((st & N.F_KEY_TOO_LONG) == 0)
     assert routable.sum() > 5000
     koff = (ar.off + o.sp1[:n] + 1).astype(np.uint64)
     klen = (o.sp2[:n] - o.sp1[:n] - 1).astype(np.uint32)
@@ -611,3 +612,55 @@ def test_c5_remap_sweep_1024_nodes(eng):
         assert 0.5 / 1024 < frac < 4.0 / 1024, frac            # removed host's share + the new host's share
         assert set(owner[moved & ~was_on_removed]) <= {hosts[-1]}   # anything else that moved went to the new host
     db.free()
+
+
+def test_header_names_lowercased_on_the_device(eng, golden):
+    """R3, key.lower() (HttpParser.py:330): the names come back lower-cased FROM THE KERNEL (no host
+    .lower() anywhere in this test) and equal the keys of the reference's own headers dict."""
+    from shellac_b200.batch import ParseOut
+    whole = golden['whole']
+    msgs = [w['msg'] for w in whole]
+    ar = eng.pack(msgs)
+    n = ar.n
+    out = ParseOut(n, ar.nbytes // 4 + 64, alloc=eng.pinned, lkeys_cap=ar.nbytes + 64)
+    pg = eng.parse(ar, out=out)
+    o = O.orc_parse(ar, lkeys=True)
+    assert int(pg.lkeys_used[0]) == int(o.lkeys_used[0]) > 10000
+    checked = mixed = 0
+    for i, w in enumerate(whole):
+        got = pg.lower_keys(i)
+        assert got == o.lower_keys(i), w['id']
+        if w['obs']['exc'] is None and w['obs']['headers_complete']:
+            assert set(k.decode('latin-1') for k in got) == set(w['obs']['headers'].keys()), w['id']
+            checked += 1
+            b, k = int(pg.hdr_base[i]), int(pg.n_headers[i])
+            raw = [ar.message(i)[int(r['key_off']):int(r['key_off']) + int(r['key_len'])] for r in pg.hdr[b:b + k]]
+            mixed += sum(x != y for x, y in zip(raw, got))
+    assert checked > 3000 and mixed > 1000          # plenty of names really had upper-case letters
+    # the fused route entry fills the same arena
+    eng.ring_build(['10.0.0.%d' % (i + 1) for i in range(16)])
+    out2 = ParseOut(n, ar.nbytes // 4 + 64, alloc=eng.pinned, lkeys_cap=ar.nbytes + 64)
+    p2, _ = eng.route(ar, pout=out2)
+    assert all(p2.lower_keys(i) == pg.lower_keys(i) for i in range(0, n, 7))
+
+
+def test_key_too_long_is_flagged_not_placed(eng):
+    """R9: the cache key is the URL (Server.py:327); pylibmc refuses keys over 250 bytes before it
+    hashes them (Server.py:335).  Such requests parse normally, carry SHL_F_KEY_TOO_LONG and get no node."""
+    hosts = ['10.0.0.%d' % (i + 1) for i in range(16)]
+    eng.ring_build(hosts)
+    lens = [1, 249, 250, 251, 252, 400, 3000]
+    msgs = [b'GET /' + b'k' * (L - 1) + b' HTTP/1.1\r\nHost: x\r\n\r\n' for L in lens]
+    msgs += [b'GET /a b' + b'k' * 300 + b' HTTP/1.1\r\nHost: x\r\n\r\n']        # the key is "/a": short
+    ar = eng.pack(msgs * 40)
+    pg, qg = eng.route(ar)
+    o = O.orc_parse(ar)
+    assert (pg.status[:ar.n] == o.status[:ar.n]).all()
+    flag = (pg.status[:ar.n] & N.F_KEY_TOO_LONG) != 0
+    want = np.array([L > N.MAX_KEY_LEN for L in lens] + [False] * 1, bool)
+    assert (flag == np.tile(want, 40)).all()
+    assert (qg.node[:ar.n][flag] == 0xffffffff).all() and (qg.node[:ar.n][~flag] < 16).all()
+    assert int(qg.hist.sum()) == int((~flag).sum())
+    for i in np.flatnonzero(~flag)[:8]:
+        key = ar.message(int(i))[int(pg.sp1[i]) + 1:int(pg.sp2[i])]
+        assert qg.digest(int(i)) == hashlib.md5(key).digest()

@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol(lib):
 
 def test_struct_layouts_match_header():
     assert N.HDR_DTYPE.itemsize == 8 and N.CHUNK_DTYPE.itemsize == 16
-    assert C.sizeof(N.ParseOutStruct) == 14 * 8
+    assert C.sizeof(N.ParseOutStruct) == 18 * 8
     assert C.sizeof(N.FrameOutStruct) == 9 * 8
     assert C.sizeof(N.PlaceOutStruct) == 4 * 8
 

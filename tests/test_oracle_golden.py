@@ -163,3 +163,20 @@ def test_oracle_body_gather_matches_reference_bodies(golden):
         assert bo.get(i) == v.raw_body(), w['id']
         if not w['obs']['exc']:
             assert bo.get(i).decode('latin-1') == w['obs']['body'], w['id']
+
+
+def test_oracle_lower_keys_and_key_too_long(golden):
+    """key.lower() (HttpParser.py:330) as the oracle emits it == the keys of the reference's headers
+    dict; SHL_F_KEY_TOO_LONG marks request URLs over 250 bytes (pylibmc's limit, Server.py:335)."""
+    whole = golden['whole']
+    ar = Arena.pack([w['msg'] for w in whole])
+    o = O.orc_parse(ar, lkeys=True)
+    n_checked = 0
+    for i, w in enumerate(whole):
+        if w['obs']['exc'] is None and w['obs']['headers_complete']:
+            assert set(k.decode('latin-1') for k in o.lower_keys(i)) == set(w['obs']['headers'].keys()), w['id']
+            n_checked += 1
+    assert n_checked > 3000
+    msgs = [b'GET /' + b'k' * (L - 1) + b' HTTP/1.1\r\nA: b\r\n\r\n' for L in (249, 250, 251)] + [b'HTTP/1.1 200 ' + b'k' * 300 + b'\r\n\r\n']
+    st = O.orc_parse(Arena.pack(msgs)).status[:4]
+    assert [bool(x & N.F_KEY_TOO_LONG) for x in st] == [False, False, True, False]

@@ -26,7 +26,7 @@ class OracleRouter(object):
         po = O.orc_parse(ar)
         fo = O.orc_frame(ar, po)
         st = po.status[:n]
-        ok = ((st & 0x400) != 0) & ((st & 0x100) != 0) & ((st & (1 << 17)) != 0) & ((st & 0xff) == 0)
+        ok = ((st & 0x400) != 0) & ((st & 0x100) != 0) & ((st & (1 << 17)) != 0) & ((st & 0xff) == 0) & ((st & (1 << 18)) == 0)
         koff = (ar.off + po.sp1[:n] + 1).astype(np.uint64)
         klen = (po.sp2[:n] - po.sp1[:n] - 1).astype(np.uint32)
         koff[~ok] = 0
