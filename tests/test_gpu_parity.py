@@ -636,7 +636,7 @@ def test_header_names_lowercased_on_the_device(eng, golden):
             b, k = int(pg.hdr_base[i]), int(pg.n_headers[i])
             raw = [ar.message(i)[int(r['key_off']):int(r['key_off']) + int(r['key_len'])] for r in pg.hdr[b:b + k]]
             mixed += sum(x != y for x, y in zip(raw, got))
-    assert checked > 3000 and mixed > 1000          # plenty of names really had upper-case letters
+    assert checked > 2500 and mixed > 1000          # plenty of names really had upper-case letters
     # the fused route entry fills the same arena
     eng.ring_build(['10.0.0.%d' % (i + 1) for i in range(16)])
     out2 = ParseOut(n, ar.nbytes // 4 + 64, alloc=eng.pinned, lkeys_cap=ar.nbytes + 64)

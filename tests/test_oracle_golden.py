@@ -176,7 +176,7 @@ def test_oracle_lower_keys_and_key_too_long(golden):
         if w['obs']['exc'] is None and w['obs']['headers_complete']:
             assert set(k.decode('latin-1') for k in o.lower_keys(i)) == set(w['obs']['headers'].keys()), w['id']
             n_checked += 1
-    assert n_checked > 3000
+    assert n_checked > 2500
     msgs = [b'GET /' + b'k' * (L - 1) + b' HTTP/1.1\r\nA: b\r\n\r\n' for L in (249, 250, 251)] + [b'HTTP/1.1 200 ' + b'k' * 300 + b'\r\n\r\n']
     st = O.orc_parse(Arena.pack(msgs)).status[:4]
     assert [bool(x & N.F_KEY_TOO_LONG) for x in st] == [False, False, True, False]
