@@ -409,22 +409,37 @@ __device__ __forceinline__ bm2 window_bits(const uint32_t c, const uint4& va, co
 }
 
 // bitmaps of span[0:nbytes) (A0 is 32-byte aligned, nbytes <= kSpanMax)
+#ifndef SHL_OPT_ROWS_AHEAD
+#define SHL_OPT_ROWS_AHEAD 2          // rows of the span in flight ahead of the one being classified
+#endif
+__device__ __forceinline__ void row_load(const uint8_t* A0, const uint32_t off, const uint32_t nbytes, uint4& a, uint4& b) {
+    a = b = make_uint4(0u, 0u, 0u, 0u);
+    if (off < nbytes) { a = __ldg(reinterpret_cast<const uint4*>(A0 + off)); b = __ldg(reinterpret_cast<const uint4*>(A0 + off + 16)); }
+}
 __device__ __forceinline__ void group_bitmaps(const uint8_t* A0, const uint32_t nbytes, bm2* bm, const int lane) {
     uint32_t prev_last = 0u;
     uint32_t boff = (uint32_t)lane * 32u;
-    uint4 va = make_uint4(0u, 0u, 0u, 0u), vb = va;
-    if (boff < nbytes) { va = __ldg(reinterpret_cast<const uint4*>(A0 + boff)); vb = __ldg(reinterpret_cast<const uint4*>(A0 + boff + 16)); }
+    uint4 va, vb, na, nb;
+    row_load(A0, boff, nbytes, va, vb);
+#if SHL_OPT_ROWS_AHEAD >= 2
+    uint4 ma, mb;
+    row_load(A0, boff + 1024u, nbytes, na, nb);
+#endif
     uint32_t w = (uint32_t)lane;
     for (; boff - (uint32_t)lane * 32u < nbytes; boff += 1024u, w += 32u) {      // warp-uniform trip count
-        uint4 na = make_uint4(0u, 0u, 0u, 0u), nb = na;
-        if (boff + 1024u < nbytes) {                                        // next row in flight
-            na = __ldg(reinterpret_cast<const uint4*>(A0 + boff + 1024u)); nb = __ldg(reinterpret_cast<const uint4*>(A0 + boff + 1040u));
-        }
+#if SHL_OPT_ROWS_AHEAD >= 2
+        row_load(A0, boff + 2048u, nbytes, ma, mb);
+#else
+        row_load(A0, boff + 1024u, nbytes, na, nb);
+#endif
         uint32_t c = __shfl_up_sync(SHL_FULL, vb.w, 1);
         if (lane == 0) c = prev_last;
         prev_last = __shfl_sync(SHL_FULL, vb.w, 31);
         bm[w] = window_bits(c, va, vb);
         va = na; vb = nb;
+#if SHL_OPT_ROWS_AHEAD >= 2
+        na = ma; nb = mb;
+#endif
     }
     if (lane == 0) { bm2 z; z.x = z.y = 0u; bm[w] = z; }                        // the word behind the last row
 }
@@ -532,16 +547,32 @@ __device__ __forceinline__ void emit_records_bm(const uint8_t* m, const bm2* bm,
                 }
             }
         };
+#ifndef SHL_OPT_DEPTH
+#define SHL_OPT_DEPTH 1               // rounds of byte peeks in flight ahead of the one being written
+#endif
         Round cur, nxt;
+#if SHL_OPT_DEPTH >= 2
+        Round nx2;
         fetch(0u, cur);
+        fetch((uint32_t)kB, nxt);
+#else
+        fetch(0u, cur);
+#endif
         int ls = h0;
         for (uint32_t k = 0; k < nh; k += kB) {
+#if SHL_OPT_DEPTH >= 2
+            fetch(k + 2u * kB, nx2);
+#else
             fetch(k + kB, nxt);
+#endif
 #pragma unroll
             for (int j = 0; j < kB; j++) {
                 if (k + (uint32_t)j < nh) { put_record(m, out, k + j, ls, cur.sep[j], cur.end[j], cur.c0[j], cur.c1[j], nc); ls = cur.end[j] + 2; }
             }
             cur = nxt;
+#if SHL_OPT_DEPTH >= 2
+            nxt = nx2;
+#endif
         }
     }
     note_names(m, out, nh, nc, wk);
