@@ -167,6 +167,9 @@ int  shl_device_count(void);
 /* "0000:1b:00.0"-style PCI address of a device (len >= 13), so that the host side can place its
  * pinned arenas on the GPU's NUMA node (shellac_b200/hostmem.py).  No reference counterpart. */
 int  shl_device_pci_bus_id(int device, char* buf, int len);
+/* Free / total device memory (cudaMemGetInfo), e.g. to size a ctx for the 180 GB of a B200 or to
+ * check that a call allocated nothing.  No reference counterpart. */
+int  shl_device_mem_info(int device, uint64_t* free_bytes, uint64_t* total_bytes);
 int  shl_ctx_create(int device, uint64_t max_msgs, uint64_t max_bytes, uint64_t max_records, shl_ctx** out);
 void shl_ctx_destroy(shl_ctx* ctx);
 const char* shl_last_error(shl_ctx* ctx);           /* ctx may be NULL: last error of ctx creation */
@@ -240,6 +243,34 @@ int  shl_body_batch(shl_ctx* ctx, uint64_t n, const shl_body_out* out);
 int  shl_group_batch(shl_ctx* ctx, uint64_t n, uint32_t* start, uint32_t* order);
 int  shl_group_dev(shl_ctx* ctx, const uint32_t* d_node, uint64_t n, uint32_t n_hosts, const uint64_t* d_hist,
                    uint32_t* d_start, uint32_t* d_cursor, uint32_t* d_order);
+/* Memcached binary-protocol request frames, grouped per node: the bytes the cache client puts on
+ * each node's socket after placement.  The reference builds its client with binary=True
+ * (pylibmc.Client(..., binary=True), Server.py:81-83) and calls get(key) at Server.py:335 and
+ * set(key, obj, time=ttl) at :432; pylibmc / libmemcached are third-party and absent, the frames
+ * follow the published protocol (24-byte header, big-endian: magic 0x80, opcode, key length,
+ * extras length, data type, vbucket, total body length, opaque, CAS).
+ *   SHL_MC_GET  header + key                       (opcode 0x00; opaque = request index)
+ *   SHL_MC_SET  header + {flags = 0, expiry = ttl} + key   (opcode 0x01); the value (the re-serialised
+ *               response) is appended by the caller; value_len[i] (per request index, may be NULL)
+ *               is counted in the total body length.
+ * Requests are taken in the node-grouped order of shl_group_*: frame j (j-th entry of order[])
+ * lies at frames[frame_off[j] : frame_off[j + 1]], so node k's stream is the contiguous range
+ * frames[frame_off[start[k]] : frame_off[start[k + 1]]].  shl_mc_frames_batch works on the batch
+ * whose shl_route_batch + shl_group_batch results are still resident on this ctx (n = batch size,
+ * n_placed = start[n_hosts]).                                                                    */
+#define SHL_MC_GET 0
+#define SHL_MC_SET 1
+typedef struct shl_mc_out {
+    uint64_t* frame_off;       /* [n_placed + 1]                                                   */
+    uint8_t*  frames;          /* byte arena, `frames_cap` bytes                                   */
+    uint64_t  frames_cap;
+    uint64_t* frames_used;     /* one element                                                      */
+} shl_mc_out;
+int  shl_mc_frames_batch(shl_ctx* ctx, uint64_t n, uint64_t n_placed, int op, uint32_t ttl,
+                         const uint32_t* value_len, const shl_mc_out* out);
+int  shl_mc_frames_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_off, const uint32_t* d_sp1,
+                       const uint32_t* d_sp2, const uint32_t* d_order, uint64_t n_placed, int op, uint32_t ttl,
+                       const uint32_t* d_value_len, const shl_mc_out* d_out);
 /* In every *_batch call `arena` may be NULL: the bytes uploaded by the previous *_batch call on
  * this ctx are reused (parse, then frame the same arena, costs one H2D copy).                    */
 
@@ -276,7 +307,10 @@ int  shl_body_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_off, c
  * host memory.  The first call on a device also resolves the array's device address; make that
  * first call before any stream capture starts.  All calls share the array, which still holds the
  * previous call's data (the histogram bins are cleared each time): calls whose GPU work overlaps
- * on one device race, so serialise them per device.                                              */
+ * on one device race, so serialise them per device.  The work runs on the device's legacy default
+ * stream: it therefore also waits for, and holds up, any BLOCKING stream another library of the
+ * process created on that device (streams made with cudaStreamNonBlocking, like every stream of
+ * this library, are not affected).  The caller's current device is restored on return.          */
 #define SHL_STATIC_MAX_KEYS       4096
 #define SHL_STATIC_MAX_KEY_BYTES  262144
 #define SHL_STATIC_MAX_POINTS     16384

@@ -250,3 +250,39 @@ def route_messages(msgs, values, nodes, n_hosts):
             hist[place(values, nodes, n_hosts, p.url)] += 1
             done += 1
     return done, hist
+
+
+# ---------------------------------------------------------------------------------------------
+# Memcached binary protocol, request side (what pylibmc.Client(..., binary=True) sends for
+# get(key) / set(key, value, time=ttl), Server.py:81-83, 335, 432).  pylibmc / libmemcached are
+# absent; restated from the published protocol: 24-byte header, network byte order.
+def mc_get_frame(key, opaque):
+    return struct.pack('>BBHBBHIIQ', 0x80, 0x00, len(key), 0, 0, 0, len(key), opaque, 0) + key
+
+
+def mc_set_header(key, opaque, value_len, ttl, flags=0):
+    """Header + extras + key of a Set; the value's bytes follow on the wire."""
+    return struct.pack('>BBHBBHIIQ', 0x80, 0x01, len(key), 8, 0, 0, 8 + len(key) + value_len, opaque, 0) + \
+        struct.pack('>II', flags, ttl) + key
+
+
+def serialize(p):
+    """HttpParser.__str__ (:111-138) on a driven PortParser, as bytes.  Header order is arrival
+    order here (Python-2 dict hash order in the reference): compare the lines as a multiset."""
+    if p.is_request:
+        s = b'%s %s HTTP/%s\r\n' % (p.method, p.url, b'%.1f' % p.version)
+    else:
+        s = b'HTTP/%s %d %s\r\n' % (b'%.1f' % p.version, p.status, p.reason)
+    p.headers.pop(b'transfer-encoding', None)
+    p.headers.pop(b'content-length', None)
+    p.body.seek(0)
+    b = p.body.read()
+    if p.headers.get(b'content-encoding', b'identity') == b'gzip':
+        zz = zlib.compressobj(6, zlib.DEFLATED, 31)
+        b = zz.compress(b) + zz.flush()
+    if len(b) != 0:
+        p.headers[b'content-length'] = len(b)
+    h = b''.join(b'%s: %s\r\n' % (b'-'.join(x.capitalize() for x in k.split(b'-')),
+                                  b', '.join(v) if isinstance(v, list) else (v if isinstance(v, bytes) else b'%d' % v))
+                 for k, v in p.headers.items())
+    return s + h + b'\r\n' + b

@@ -28,6 +28,7 @@ F_KEY_TOO_LONG = 1 << 18
 MAX_KEY_LEN = 250
 FS_NOT_CHUNKED = 0xff
 RING_KETAMA, RING_KETAMA_WEIGHTED = 0, 1
+MC_GET, MC_SET = 0, 1
 N_CODES = 64          # SHL_N_CODES: histogram length for per-outcome counts
 COMM_ID_BYTES = 128   # SHL_COMM_ID_BYTES
 
@@ -70,6 +71,10 @@ class BodyOutStruct(C.Structure):
                 ('body_cap', C.c_uint64), ('body_used', C.c_void_p)]
 
 
+class McOutStruct(C.Structure):
+    _fields_ = [('frame_off', C.c_void_p), ('frames', C.c_void_p), ('frames_cap', C.c_uint64), ('frames_used', C.c_void_p)]
+
+
 class PlaceOutStruct(C.Structure):
     _fields_ = [('md5', C.c_void_p), ('hash', C.c_void_p), ('node', C.c_void_p), ('hist', C.c_void_p)]
 
@@ -101,6 +106,7 @@ def lib():
     vp, u64, i32 = C.c_void_p, C.c_uint64, C.c_int
     sig = {
         'shl_device_count': (i32, []),
+        'shl_device_mem_info': (i32, [i32, _u64p, _u64p]),
         'shl_device_pci_bus_id': (i32, [i32, C.c_char_p, i32]),
         'shl_ctx_create': (i32, [i32, u64, u64, u64, C.POINTER(vp)]),
         'shl_ctx_destroy': (None, [vp]),
@@ -128,6 +134,8 @@ def lib():
         'shl_body_dev': (i32, [vp, vp, vp, vp, u64, C.POINTER(ParseOutStruct), C.POINTER(FrameOutStruct), C.POINTER(BodyOutStruct)]),
         'shl_group_batch': (i32, [vp, u64, vp, vp]),
         'shl_group_dev': (i32, [vp, vp, u64, C.c_uint32, vp, vp, vp, vp]),
+        'shl_mc_frames_batch': (i32, [vp, u64, u64, i32, C.c_uint32, vp, C.POINTER(McOutStruct)]),
+        'shl_mc_frames_dev': (i32, [vp, vp, vp, vp, vp, vp, u64, i32, C.c_uint32, vp, C.POINTER(McOutStruct)]),
         'shl_chunk_header_batch': (i32, [vp, vp, u64, vp, vp, u64, vp, vp, vp]),
         'shl_parse_dev': (i32, [vp, vp, vp, vp, u64, C.POINTER(ParseOutStruct)]),
         'shl_frame_dev': (i32, [vp, vp, vp, vp, u64, vp, vp, vp, C.POINTER(FrameOutStruct)]),

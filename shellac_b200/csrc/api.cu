@@ -59,6 +59,8 @@ struct shl_ctx {
     ncclComm_t comm = nullptr; int comm_rank = 0, comm_world = 1;
     uint64_t* d_scratch = nullptr; uint64_t* h_scratch = nullptr;             // 64 words for shl_comm_allreduce_u64
     uint64_t cur_n = 0;                   // messages of the last *_batch parse (frame_batch checks it)
+    uint64_t* d_mc_off = nullptr; uint64_t* d_mc_sums = nullptr; uint8_t* d_mc_frames = nullptr; uint32_t* d_mc_vlen = nullptr;   // memcached frames (lazy)
+    uint64_t mc_frames_cap = 0;
     uint8_t* d_lkeys = nullptr; uint32_t* d_lkey_base = nullptr;   // lower-cased header names (lazy; d_counters[2] counts the bytes)
     int force_scalar = 0;
     int sm_count = 148, grid_waves = 16;
@@ -200,6 +202,17 @@ int shl_device_count(void) {
     return n;
 }
 
+int shl_device_mem_info(int device, uint64_t* free_bytes, uint64_t* total_bytes) {
+    shl_ctx* ctx = nullptr;
+    DeviceGuard guard;
+    CU(guard.enter(device));
+    size_t f = 0, t = 0;
+    CU(cudaMemGetInfo(&f, &t));
+    if (free_bytes) *free_bytes = f;
+    if (total_bytes) *total_bytes = t;
+    return SHL_OK;
+}
+
 int shl_device_pci_bus_id(int device, char* buf, int len) {
     if (!buf || len < 13) return -1;
     return cudaDeviceGetPCIBusId(buf, len, device) == cudaSuccess ? 0 : -2;
@@ -308,6 +321,7 @@ void shl_ctx_destroy(shl_ctx* ctx) {
     cudaFree(ctx->d_ring_values); cudaFree(ctx->d_ring_nodes); cudaFree(ctx->d_ring_dir); cudaFree(ctx->d_hist);
     cudaFree(ctx->d_body); cudaFree(ctx->d_body_off); cudaFree(ctx->d_body_len);
     cudaFree(ctx->d_lkeys); cudaFree(ctx->d_lkey_base);
+    cudaFree(ctx->d_mc_off); cudaFree(ctx->d_mc_sums); cudaFree(ctx->d_mc_frames); cudaFree(ctx->d_mc_vlen);
     cudaFree(ctx->d_gstart); cudaFree(ctx->d_gcursor); cudaFree(ctx->d_gorder);
     for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
     for (auto& st : ctx->pipe) if (st) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
@@ -943,6 +957,57 @@ int shl_group_batch(shl_ctx* ctx, uint64_t n, uint32_t* start, uint32_t* order) 
     if (int rc = shl_group_dev(ctx, ctx->cur_node, n, ctx->n_hosts, ctx->cur_hist, ctx->d_gstart, ctx->d_gcursor, ctx->d_gorder)) return rc;
     CU(cudaMemcpyAsync(start, ctx->d_gstart, (size_t)(ctx->n_hosts + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaMemcpyAsync(order, ctx->d_gorder, n * 4, cudaMemcpyDeviceToHost, ctx->stream));   // only start[n_hosts] entries are meaningful
+    return SHL_OK;
+}
+
+// ---- memcached binary-protocol frames per node (what pylibmc sends behind Server.py:335 / :432)
+int shl_mc_frames_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_off, const uint32_t* d_sp1, const uint32_t* d_sp2,
+                      const uint32_t* d_order, uint64_t n_placed, int op, uint32_t ttl, const uint32_t* d_value_len,
+                      const shl_mc_out* d_out) {
+    if (!ctx || !d_arena || !d_off || !d_sp1 || !d_sp2 || !d_order || !d_out || !d_out->frame_off || !d_out->frames || !d_out->frames_used)
+        return fail(ctx, SHL_ERR_ARG, "shl_mc_frames_dev: null pointer");
+    if (op != SHL_MC_GET && op != SHL_MC_SET) return fail(ctx, SHL_ERR_ARG, "shl_mc_frames_dev: op is SHL_MC_GET or SHL_MC_SET");
+    CU(cudaSetDevice(ctx->device));
+    if (n_placed > ctx->max_msgs) return fail(ctx, SHL_ERR_ARG, "shl_mc_frames_dev: more requests than the ctx was created for");
+    if (!ctx->d_mc_sums) CU(dalloc(&ctx->d_mc_sums, ctx->max_msgs / shl::kMcScanItems + 2));
+    shl::McArgs a{};
+    a.arena = d_arena; a.off = d_off; a.sp1 = d_sp1; a.sp2 = d_sp2; a.order = d_order; a.n = n_placed;
+    a.value_len = d_value_len; a.op = (uint32_t)op; a.ttl = ttl;
+    a.frame_off = d_out->frame_off; a.block_sums = ctx->d_mc_sums;
+    a.frames = d_out->frames; a.frames_cap = d_out->frames_cap; a.frames_used = d_out->frames_used;
+    const unsigned nb = (unsigned)((n_placed + shl::kMcScanItems - 1) / shl::kMcScanItems);
+    if (nb) shl::k_mc_sizes<<<nb, 256, 0, ctx->stream>>>(a);
+    shl::k_mc_block_scan<<<1, 1024, 0, ctx->stream>>>(ctx->d_mc_sums, nb, a.frames_used, a.frame_off, n_placed);
+    if (n_placed) shl::k_mc_emit<<<(unsigned)((n_placed * 32 + 255) / 256), 256, 0, ctx->stream>>>(a);
+    ctx->launches += nb ? 3 : 1;
+    CU(cudaGetLastError());
+    return SHL_OK;
+}
+
+int shl_mc_frames_batch(shl_ctx* ctx, uint64_t n, uint64_t n_placed, int op, uint32_t ttl, const uint32_t* value_len,
+                        const shl_mc_out* out) {
+    if (!ctx || !out || !out->frame_off) return fail(ctx, SHL_ERR_ARG, "shl_mc_frames_batch: null pointer");
+    if (!ctx->d_gorder || !ctx->cur_node) return fail(ctx, SHL_ERR_ARG, "shl_mc_frames_batch needs a preceding shl_route_batch + shl_group_batch");
+    if (n > ctx->max_msgs || n_placed > n) return fail(ctx, SHL_ERR_ARG, "shl_mc_frames_batch: bad counts");
+    CU(cudaSetDevice(ctx->device));
+    const uint64_t cap = ctx->max_bytes + 32 * ctx->max_msgs;
+    if (!ctx->d_mc_frames) {
+        CU(dalloc(&ctx->d_mc_off, ctx->max_msgs + 1)); CU(dalloc(&ctx->d_mc_frames, cap)); CU(dalloc(&ctx->d_mc_vlen, ctx->max_msgs));
+        ctx->mc_frames_cap = cap;
+    }
+    if (value_len) CU(cudaMemcpyAsync(ctx->d_mc_vlen, value_len, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    shl_mc_out d{};
+    d.frame_off = ctx->d_mc_off; d.frames = ctx->d_mc_frames; d.frames_cap = ctx->mc_frames_cap; d.frames_used = ctx->d_counters + 3;
+    if (int rc = shl_mc_frames_dev(ctx, ctx->d_arena, ctx->d_off, ctx->cur_dp.sp1, ctx->cur_dp.sp2, ctx->d_gorder, n_placed, op, ttl,
+                                   value_len ? ctx->d_mc_vlen : nullptr, &d)) return rc;
+    CU(cudaMemcpyAsync(out->frame_off, ctx->d_mc_off, (n_placed + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->h_counters + 3, ctx->d_counters + 3, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    const uint64_t used = ctx->h_counters[3];
+    if (out->frames_used) *out->frames_used = used;
+    if (used > ctx->mc_frames_cap || (out->frames && used > out->frames_cap))
+        return fail(ctx, SHL_ERR_CAPACITY, "memcached frame arena overflowed: raise frames_cap");
+    if (out->frames && used) CU(cudaMemcpyAsync(out->frames, ctx->d_mc_frames, used, cudaMemcpyDeviceToHost, ctx->stream));
     return SHL_OK;
 }
 

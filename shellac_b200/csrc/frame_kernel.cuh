@@ -379,3 +379,113 @@ __global__ void __launch_bounds__(256) k_group_scatter(const uint32_t* __restric
 }
 
 }  // namespace shl
+
+// ----------------------------------------------------------------------------------- N3: memcached binary frames
+// What leaves the proxy for each memcached node after placement: the reference's client is built
+// with binary=True (pylibmc.Client(..., binary=True), Server.py:81-83) and issues get(key) at
+// Server.py:335 and set(key, obj, time=ttl) at :432.  pylibmc / libmemcached are third-party and
+// absent here; the frames follow the memcached binary protocol as published (24-byte header:
+// magic 0x80, opcode, key length, extras length, data type, vbucket, total body length, opaque,
+// CAS; big-endian fields) — restated in oracle/py_port.py (mc_get_frame / mc_set_header).
+//   op 0  get : header + key                                   (opcode 0x00)
+//   op 1  set : header + extras {flags u32 = 0, expiry u32 = ttl} + key; the VALUE (the re-serialised
+//               response, HttpParser.__str__) is appended by the caller: total body counts it.
+// Requests come in the node-grouped order of k_group_scatter, so node k's stream is one contiguous
+// range of the output: frames[frame_off[start[k]] : frame_off[start[k + 1]]].
+namespace shl {
+
+constexpr int kMcScanItems = 2048;              // requests per block of the size scan (256 threads x 8)
+
+struct McArgs {
+    const uint8_t* arena; const uint64_t* off; const uint32_t* sp1; const uint32_t* sp2;
+    const uint32_t* order; uint64_t n;          // n = requests that have a node (start[n_hosts])
+    const uint32_t* value_len;                  // op 1: bytes of the value that will follow each frame, per REQUEST index (may be null: 0)
+    uint32_t op, ttl;
+    uint64_t* frame_off;                        // [n + 1]
+    uint64_t* block_sums;                       // [ceil(n / kMcScanItems) + 1] scratch
+    uint8_t* frames; uint64_t frames_cap; uint64_t* frames_used;
+};
+
+__device__ __forceinline__ uint32_t mc_frame_bytes(const McArgs& a, uint64_t j) {
+    const uint32_t i = a.order[j];
+    return 24u + (a.op ? 8u : 0u) + (a.sp2[i] - a.sp1[i] - 1u);
+}
+
+// pass 1: per-block exclusive scan of the frame sizes (local offsets) + the block's total
+__global__ void __launch_bounds__(256) k_mc_sizes(const McArgs a) {
+    __shared__ uint32_t warp_sum[8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint64_t base = (uint64_t)blockIdx.x * kMcScanItems + (uint64_t)threadIdx.x * 8u;
+    uint32_t v[8], sum = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) { v[k] = base + k < a.n ? mc_frame_bytes(a, base + k) : 0u; sum += v[k]; }
+    uint32_t inc = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(SHL_FULL, inc, d); if (lane >= d) inc += t; }
+    if (lane == 31) warp_sum[warp] = inc;
+    __syncthreads();
+    uint32_t wbase = 0;
+    for (int w = 0; w < warp; w++) wbase += warp_sum[w];
+    uint32_t run = wbase + inc - sum;
+#pragma unroll
+    for (int k = 0; k < 8; k++) { if (base + k < a.n) a.frame_off[base + k] = run; run += v[k]; }
+    if (threadIdx.x == 255) a.block_sums[blockIdx.x] = run;
+}
+// pass 2: one block turns the block totals into block bases (exclusive), total at [nblocks]
+__global__ void __launch_bounds__(1024) k_mc_block_scan(uint64_t* __restrict__ sums, uint32_t nblocks, uint64_t* __restrict__ used,
+                                                        uint64_t* __restrict__ frame_off, uint64_t n) {
+    __shared__ unsigned long long part[1024];
+    const uint32_t per = (nblocks + 1023u) / 1024u;
+    const uint32_t lo = threadIdx.x * per, hi = min(nblocks, lo + per);
+    unsigned long long s = 0;
+    for (uint32_t b = lo; b < hi; b++) s += sums[b];
+    part[threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) { unsigned long long run = 0; for (int t = 0; t < 1024; t++) { const unsigned long long x = part[t]; part[t] = run; run += x; } *used = run; frame_off[n] = run; }
+    __syncthreads();
+    unsigned long long run = part[threadIdx.x];
+    for (uint32_t b = lo; b < hi; b++) { const unsigned long long x = sums[b]; sums[b] = run; run += x; }
+}
+// pass 3: one warp per request writes its frame (lanes 0..23 / 0..31 the header + extras, then the key)
+__global__ void __launch_bounds__(256) k_mc_emit(const McArgs a) {
+    const uint64_t j = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (j >= a.n) return;
+    const uint32_t i = a.order[j];
+    const uint32_t klen = a.sp2[i] - a.sp1[i] - 1u, ext = a.op ? 8u : 0u;
+    const uint64_t at = a.frame_off[j] + a.block_sums[j / kMcScanItems];
+    __syncwarp();
+    if (lane == 0) a.frame_off[j] = at;
+    const uint32_t hdr = 24u + ext;
+    if (at + hdr + klen > a.frames_cap) return;
+    const uint32_t body = ext + klen + (a.op && a.value_len ? a.value_len[i] : 0u);
+    uint8_t* f = a.frames + at;
+    if ((uint32_t)lane < hdr) {
+        uint32_t b = 0;
+        switch (lane) {
+            case 0: b = 0x80u; break;                      // magic: request
+            case 1: b = a.op ? 0x01u : 0x00u; break;       // opcode: Get / Set
+            case 2: b = klen >> 8; break;                  // key length, big-endian
+            case 3: b = klen & 0xffu; break;
+            case 4: b = ext; break;                        // extras length
+            case 8: b = body >> 24; break;                 // total body length
+            case 9: b = (body >> 16) & 0xffu; break;
+            case 10: b = (body >> 8) & 0xffu; break;
+            case 11: b = body & 0xffu; break;
+            case 12: b = i >> 24; break;                   // opaque = request index: pairs the reply with the request
+            case 13: b = (i >> 16) & 0xffu; break;
+            case 14: b = (i >> 8) & 0xffu; break;
+            case 15: b = i & 0xffu; break;
+            case 28: b = a.ttl >> 24; break;               // set extras: flags (0) then expiry
+            case 29: b = (a.ttl >> 16) & 0xffu; break;
+            case 30: b = (a.ttl >> 8) & 0xffu; break;
+            case 31: b = a.ttl & 0xffu; break;
+            default: b = 0; break;                         // data type, vbucket, CAS, flags
+        }
+        f[lane] = (uint8_t)b;
+    }
+    const uint8_t* key = a.arena + a.off[i] + a.sp1[i] + 1u;
+    for (uint32_t k = (uint32_t)lane; k < klen; k += 32u) f[hdr + k] = (uint8_t)ldb(key + k);
+}
+
+}  // namespace shl

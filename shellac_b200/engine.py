@@ -34,7 +34,9 @@ class Engine(object):
 
     # -- memory -----------------------------------------------------------------------------
     def pinned(self, n, dtype):
-        """A page-locked numpy array (zero-filled) that lives as long as the engine."""
+        """A page-locked numpy array (zero-filled) that lives as long as the engine.  The calls
+        below that are not given `out=` allocate their result arrays this way on EVERY call: a
+        long-lived caller passes `out=` (see PinnedBatch) or frees with release_pinned(mark)."""
         dt = np.dtype(dtype)
         nbytes = max(int(n), 1) * dt.itemsize
         p = C.c_void_p()
@@ -171,10 +173,35 @@ class Engine(object):
     def group(self, n):
         """Requests of the batch just routed/placed (with a histogram), grouped by node:
         (start[n_hosts + 1], order[n]); node k owns order[start[k]:start[k + 1]]."""
-        start, order = self.pinned(self.n_hosts + 1, np.uint32), self.pinned(n, np.uint32)
+        g = getattr(self, '_group_bufs', None)          # pinned outputs are kept and only grow (a reactor calls this every tick)
+        if g is None or len(g[0]) < self.n_hosts + 1 or len(g[1]) < n:
+            g = (self.pinned(max(self.n_hosts + 1, 64), np.uint32), self.pinned(max(n, 1024), np.uint32))
+            self._group_bufs = g
+        start, order = g[0][:self.n_hosts + 1], g[1]
         _check(self.lib, self.ctx, self.lib.shl_group_batch(self.ctx, n, start.ctypes.data, order.ctypes.data), 'shl_group_batch')
         self.sync()
         return start, order[:n]
+
+    def mc_frames(self, n, n_placed, op=N.MC_GET, ttl=0, value_len=None, frames_cap=0):
+        """Memcached binary-protocol request frames of the batch just routed + grouped, in the
+        node-grouped order: (frame_off[n_placed + 1], frames bytes).  Node k's stream is
+        frames[frame_off[start[k]]:frame_off[start[k + 1]]] with `start` from group()."""
+        cap = int(frames_cap) if frames_cap else self.max_bytes + 32 * self.max_msgs
+        bufs = getattr(self, '_mc_bufs', None)
+        if bufs is None or bufs[0] < n_placed + 1 or bufs[1] < cap:
+            bufs = (max(n_placed + 1, 1024), cap, self.pinned(max(n_placed + 1, 1024), np.uint64), self.pinned(cap, np.uint8),
+                    self.pinned(1, np.uint64))
+            self._mc_bufs = bufs
+        _, _, foff, frames, used = bufs
+        s = N.McOutStruct()
+        s.frame_off, s.frames, s.frames_cap, s.frames_used = foff.ctypes.data, frames.ctypes.data, cap, used.ctypes.data
+        vl = None
+        if value_len is not None:
+            vl = np.ascontiguousarray(value_len, dtype=np.uint32)
+        rc = self.lib.shl_mc_frames_batch(self.ctx, n, n_placed, op, ttl, vl.ctypes.data if vl is not None else None, C.byref(s))
+        _check(self.lib, self.ctx, rc, 'shl_mc_frames_batch')
+        self.sync()
+        return foff[:n_placed + 1], frames[:int(used[0])]
 
     def chunk_header(self, arena, out=None):
         n = arena.n

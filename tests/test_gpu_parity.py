@@ -664,3 +664,39 @@ def test_key_too_long_is_flagged_not_placed(eng):
     for i in np.flatnonzero(~flag)[:8]:
         key = ar.message(int(i))[int(pg.sp1[i]) + 1:int(pg.sp2[i])]
         assert qg.digest(int(i)) == hashlib.md5(key).digest()
+
+
+def test_memcached_frames_per_node(eng, golden):
+    """N3: get / set request frames of the memcached binary protocol, one contiguous stream per node
+    (what pylibmc sends behind Server.py:335 / :432), against the struct.pack restatement."""
+    import os, sys
+    sys.path.insert(0, os.path.join(O.ROOT, 'oracle'))
+    import py_port
+    hosts = ['10.0.0.%d' % (i + 1) for i in range(16)]
+    eng.ring_build(hosts)
+    c2 = eng.corpus_host(20130725, 31000, 6000, 0)
+    msgs = [c2.message(i) for i in range(6000)] + [w['msg'] for w in golden['whole'][:1500]]
+    ar = eng.pack(msgs)
+    n = ar.n
+    pg, qg = eng.route(ar)
+    start, order = eng.group(n)
+    n_placed = int(start[len(hosts)])
+    assert n_placed > 6000
+    foff, frames = eng.mc_frames(n, n_placed, N.MC_GET)
+    blob = frames.tobytes()
+    assert int(foff[n_placed]) == len(blob)
+    for k in range(len(hosts)):                                  # node k's stream: its requests' frames back to back
+        want = b''
+        for j in range(int(start[k]), int(start[k + 1])):
+            i = int(order[j])
+            key = ar.message(i)[int(pg.sp1[i]) + 1:int(pg.sp2[i])]
+            assert int(qg.node[i]) == k
+            want += py_port.mc_get_frame(key, i)
+        assert blob[int(foff[start[k]]):int(foff[start[k + 1]])] == want, k
+    vlen = (np.arange(n, dtype=np.uint32) * 37) % 5000
+    foff, frames = eng.mc_frames(n, n_placed, N.MC_SET, ttl=170, value_len=vlen)       # ttl default of the reference CLI (Server.py:510)
+    blob = frames.tobytes()
+    for j in list(range(0, n_placed, 97)) + [n_placed - 1]:
+        i = int(order[j])
+        key = ar.message(i)[int(pg.sp1[i]) + 1:int(pg.sp2[i])]
+        assert blob[int(foff[j]):int(foff[j + 1])] == py_port.mc_set_header(key, i, int(vlen[i]), 170), j

@@ -180,3 +180,16 @@ def test_oracle_lower_keys_and_key_too_long(golden):
     msgs = [b'GET /' + b'k' * (L - 1) + b' HTTP/1.1\r\nA: b\r\n\r\n' for L in (249, 250, 251)] + [b'HTTP/1.1 200 ' + b'k' * 300 + b'\r\n\r\n']
     st = O.orc_parse(Arena.pack(msgs)).status[:4]
     assert [bool(x & N.F_KEY_TOO_LONG) for x in st] == [False, False, True, False]
+
+
+def test_memcached_frame_restatement_known_answers():
+    """The binary-protocol restatement against the protocol document's own examples ("Get" of key
+    'Hello'; "Set"-shaped header arithmetic)."""
+    import sys, os
+    sys.path.insert(0, os.path.join(O.ROOT, 'oracle'))
+    import py_port
+    assert py_port.mc_get_frame(b'Hello', 0) == bytes.fromhex('80000005000000000000000500000000' '0000000000000000') + b'Hello'
+    h = py_port.mc_set_header(b'Hello', 0xdeadbeef, 5, 0x0e10, flags=0xdeadbeef)
+    # the document's "Add" example carries flags 0xdeadbeef, expiry 0x0e10, key Hello, value World: body 0x12
+    assert h[2:4] == b'\x00\x05' and h[4] == 8 and h[8:12] == b'\x00\x00\x00\x12' and h[24:32] == bytes.fromhex('deadbeef00000e10')
+    assert h[32:] == b'Hello' and h[12:16] == bytes.fromhex('deadbeef') and h[1] == 1

@@ -13,6 +13,7 @@ see any of it.  The file name sorts last so a `pytest -x` run has already execut
 when it gets here; it must also pass alone in a fresh process.
 """
 import ctypes as C
+import hashlib
 
 import numpy as np
 import pytest
@@ -55,12 +56,55 @@ def test_static_placement_matches_ctx_placement_twice_in_a_row():
         ref = eng.place(eng.pack(keys))
         batches.append((ar, ref.md5[:16 * n].copy(), ref.hash[:n].copy(), ref.node[:n].copy(), ref.hist.copy()))
     eng.close()
+    free0 = _free_bytes(lib)
     for ar, e_md5, e_hash, e_node, e_hist in batches:        # two calls in a row through the C ABI
         md5, hsh, node, hist = _static_place(lib, ar, vals, nodes, len(hosts))
         assert (md5 == e_md5).all()
         assert (hsh == e_hash).all()
         assert (node == e_node).all()
         assert hist.tolist() == e_hist.tolist() and int(hist.sum()) == ar.n
+        # ... and against an expectation that shares no code with the library: hashlib + searchsorted
+        keys = [ar.message(i) for i in range(ar.n)]
+        dig = [hashlib.md5(k).digest() for k in keys]
+        assert md5.tobytes() == b''.join(dig)
+        h = np.array([int.from_bytes(d[:4], 'little') for d in dig], np.uint32)
+        j = np.searchsorted(vals, h, side='left')
+        assert (node == nodes[np.where(j == len(vals), 0, j)]).all() and (hsh == h).all()
+    # the property in the entry point's name: the calls left the device's free memory where it was
+    assert _free_bytes(lib) == free0
+
+
+def _free_bytes(lib):
+    free, total = C.c_uint64(), C.c_uint64()
+    assert lib.shl_device_mem_info(0, C.byref(free), C.byref(total)) == 0
+    return free.value
+
+
+def test_static_placement_edges():
+    """No keys at all, a ring of one host, and a histogram that already holds counts (it is added to)."""
+    from shellac_b200 import build as B
+    B.build()
+    lib = N.lib()
+    vals = (np.arange(1, 201, dtype=np.uint64) * 21000000).astype(np.uint32)
+    nodes = (np.arange(200) % 4).astype(np.uint32)
+    keys = [b'/k%d' % i for i in range(300)]
+    ar = Arena.pack(keys)
+    md5, hsh, node, hist = _static_place(lib, ar, vals, nodes, 4)
+    again = np.full(4, 7, np.uint64)                          # pre-filled: counts are ADDED
+    rc = lib.shl_place_static(0, ar.data.ctypes.data, ar.nbytes, ar.off.ctypes.data, ar.len.ctypes.data, ar.n,
+                              vals.ctypes.data, nodes.ctypes.data, len(vals), 4, None, None, None, again.ctypes.data)
+    assert rc == 0 and (again == hist + 7).all()
+    h = np.array([int.from_bytes(hashlib.md5(k).digest()[:4], 'little') for k in keys], np.uint32)
+    j = np.searchsorted(vals, h, side='left')
+    assert (node == nodes[np.where(j == len(vals), 0, j)]).all()
+    empty = Arena.pack([])
+    e_hist = np.full(4, 3, np.uint64)
+    rc = lib.shl_place_static(0, ar.data.ctypes.data, 0, empty.off.ctypes.data, empty.len.ctypes.data, 0,
+                              vals.ctypes.data, nodes.ctypes.data, len(vals), 4, None, None, None, e_hist.ctypes.data)
+    assert rc == 0 and (e_hist == 3).all()                    # nothing placed, nothing touched
+    one = np.zeros(len(vals), np.uint32)
+    _, _, node1, hist1 = _static_place(lib, ar, vals, one, 1)  # libmemcached: a single host takes every key
+    assert (node1 == 0).all() and hist1.tolist() == [len(keys)]
 
 
 def test_static_placement_refuses_oversize_inputs():
