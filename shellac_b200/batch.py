@@ -320,6 +320,10 @@ class MessageView(object):
         (HttpParser.py:213-214 and :296-297)."""
         if not self._body_call():
             return b''
+        rows = self.p
+        if getattr(rows, 'body', None) is not None:             # gathered on the device (shl_body_batch)
+            o = int(rows.body_off[self.i])
+            return rows.body[o:o + int(rows.body_len[self.i])].tobytes()
         if self.chunked():
             return b''.join(self.m[d:d + n] for (_, _, d, n) in self.chunks())
         if not self.message_complete():

@@ -335,6 +335,14 @@ class PinnedBatch(object):
             self.qout = PlaceOut(self._cap_n, max(eng.n_hosts, 1), alloc=eng.pinned)
             self._hosts = eng.n_hosts
 
+    def bout(self, cap):
+        """Pinned body-gather outputs, kept and only growing."""
+        b = getattr(self, '_bout', None)
+        if b is None or b.body_cap < cap or b.n < self._cap_n:
+            b = BodyOut(self._cap_n, max(cap, 1 << 16), alloc=self.eng.pinned)
+            self._bout = b
+        return b
+
     @property
     def fout(self):
         if self._fout is None:

@@ -47,9 +47,22 @@ class DeviceBackend(object):
         ar = pb.pack(bufs)
         po = eng.parse(ar, out=pb.pout)
         fo = None
-        if frame and len(bufs) and ((po.status[:ar.n] & N.F_CHUNKED) != 0).any():
+        n = ar.n
+        st = po.status[:n]
+        chunked = frame and n and ((st & N.F_CHUNKED) != 0).any()
+        # a message has body bytes when its headers are done and something follows them
+        bodies = frame and n and (((st & N.F_HEADERS_COMPLETE) != 0) &
+                                  (ar.len[:n] > po.first_line_len[:n] + po.headers_len[:n])).any()
+        if chunked or bodies:
             fo = eng.frame(ar, po, reuse_arena=True, out=pb.fout, chunk_cap=pb.fout.chunk_cap)
-        return detach_parse(po, ar.n), (detach_frame(fo, ar.n) if fo is not None else None)
+        rows = detach_parse(po, n)
+        if bodies:
+            # N1: the bodies are gathered on the device (de-chunked / Content-Length slices, one
+            # contiguous body per message) instead of being sliced out of the message on the host
+            bo = eng.body(ar, out=pb.bout(ar.nbytes + 16 * n + 64))
+            used = int(bo.body_used[0])
+            rows.body_off, rows.body_len, rows.body = bo.body_off[:n].copy(), bo.body_len[:n].copy(), bo.body[:used].copy()
+        return rows, (detach_frame(fo, n) if (fo is not None and chunked) else None)
 
     def views(self, bufs, frame=False):
         """MessageView per buffer (bytes)."""
