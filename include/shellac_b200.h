@@ -365,6 +365,10 @@ int   shl_stats_join(shl_ctx* ctx);
 int   shl_stats_fetch(shl_ctx* ctx, uint64_t* out, uint32_t n);
 int   shl_comm_allreduce_u64(shl_ctx* ctx, uint64_t* vals, uint32_t n, int op);
 
+/* Test hook: in a library built with -DSHL_BOUNDS_CHECK the kernels count every index that falls
+ * outside its shared-memory bitmap / record slot; this returns the count so far (-1: the checks are
+ * compiled out, as in the shipped build).  No reference counterpart. */
+int   shl_debug_oob_count(void);
 /* Test hook: route every message through the scalar (non-vectorised) device path. */
 int   shl_set_force_scalar(shl_ctx* ctx, int on);
 

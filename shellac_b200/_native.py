@@ -147,6 +147,7 @@ def lib():
         'shl_code_hist_dev': (vp, [vp]),
         'shl_node_hist_dev': (vp, [vp]),
         'shl_set_force_scalar': (i32, [vp, i32]),
+        'shl_debug_oob_count': (i32, []),
         'shl_stats_dev': (vp, [vp]),
         'shl_stats_len': (C.c_uint32, [vp]),
         'shl_comm_unique_id': (i32, [vp, C.c_uint32]),

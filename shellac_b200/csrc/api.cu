@@ -1036,6 +1036,17 @@ int shl_code_hist(shl_ctx* ctx, uint64_t* out64, int reset) {
 }
 void* shl_code_hist_dev(shl_ctx* ctx) { return ctx ? (void*)cur_codes(ctx) : nullptr; }
 void* shl_node_hist_dev(shl_ctx* ctx) { return ctx ? (void*)ctx->d_hist : nullptr; }
+// Test hook of the -DSHL_BOUNDS_CHECK build: out-of-bounds indices counted by the kernels so far
+// (-1 in a build without the checks).
+int shl_debug_oob_count(void) {
+#ifdef SHL_BOUNDS_CHECK
+    unsigned int v = 0;
+    if (cudaMemcpyFromSymbol(&v, shl::g_shl_oob, sizeof v) != cudaSuccess) return -2;
+    return (int)v;
+#else
+    return -1;
+#endif
+}
 int shl_set_force_scalar(shl_ctx* ctx, int on) { if (!ctx) return SHL_ERR_ARG; ctx->force_scalar = on ? 1 : 0; return SHL_OK; }
 
 // ------------------------------------------------------------------------------------ counters across GPUs

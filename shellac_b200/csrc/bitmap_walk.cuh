@@ -38,6 +38,21 @@ SHL_BW int bw_ffs(uint32_t x) { return __builtin_ffs((int)x); }
 SHL_BW int bw_popc(uint32_t x) { return __builtin_popcount(x); }
 #endif
 
+// Bounds checks of our own (compute-sanitizer is not available on every pool): a build with
+// -DSHL_BOUNDS_CHECK counts every shared-memory bitmap index and record slot that falls outside its
+// array in g_shl_oob (read back with shl_debug_oob_count); the shipped build compiles them away.
+#if defined(SHL_BOUNDS_CHECK) && defined(__CUDACC__)
+__device__ unsigned int g_shl_oob;
+#endif
+#if defined(SHL_BOUNDS_CHECK) && defined(__CUDA_ARCH__)
+#define SHL_CHK(cond) do { if (!(cond)) atomicAdd(&g_shl_oob, 1u); } while (0)
+#else
+#define SHL_CHK(cond) do { } while (0)
+#endif
+#ifndef SHL_BM_WORDS_FOR_CHECK
+#define SHL_BM_WORDS_FOR_CHECK 0xffffffffu
+#endif
+
 struct alignas(8) bm2 { uint32_t x, y; };      // x: CRLF bits, y: ": " bits of 32 pair starts (layout of a uint2)
 
 constexpr uint32_t kBmNone = 0xffffffffu;
@@ -59,6 +74,7 @@ SHL_BW void bm_walk(const bm2* bm, const uint32_t s0, const int L, BmWalk& o) {
     uint32_t w = qlo >> 5;
     bm2 cur = bm[w];
     uint32_t c = cur.x & (0xffffffffu << (qlo & 31u)) & (w == wl ? mhi : 0xffffffffu);
+    SHL_CHK(wl < SHL_BM_WORDS_FOR_CHECK);
     while (!c && w < wl) { w++; cur = bm[w]; c = cur.x & (w == wl ? mhi : 0xffffffffu); }
     if (!c) return;                                                  // no CRLF at all
     const uint32_t b = (uint32_t)bw_ffs(c) - 1u;
@@ -149,7 +165,7 @@ SHL_BW void evc_init(EvCursor& c, const bm2* bm, const uint32_t q) {            
     c.nxt = b.x | b.y;
 }
 SHL_BW uint32_t evc_pop(EvCursor& c, const bm2* bm) {
-    while (!c.bits) { c.w++; c.bits = c.nxt; const bm2 b = bm[c.w + 1u]; c.nxt = b.x | b.y; }
+    while (!c.bits) { c.w++; SHL_CHK(c.w + 1u < SHL_BM_WORDS_FOR_CHECK); c.bits = c.nxt; const bm2 b = bm[c.w + 1u]; c.nxt = b.x | b.y; }
     const uint32_t b = (uint32_t)bw_ffs(c.bits) - 1u;
     c.bits &= c.bits - 1u;
     return (c.w << 5) + b;

@@ -24,6 +24,10 @@
 #pragma once
 #include <cuda_fp16.h>
 #include "shl_device.cuh"
+#ifndef SHL_OPT_SPANMAX
+#define SHL_OPT_SPANMAX 20480         // bytes of span a warp keeps bitmaps for (config 2: 16.4 KiB +- 0.4)
+#endif
+#define SHL_BM_WORDS_FOR_CHECK (SHL_OPT_SPANMAX / 32u + 2u)
 #include "bitmap_walk.cuh"
 
 namespace shl {
@@ -367,9 +371,6 @@ __device__ __forceinline__ uint32_t count_lines(const uint16_t* cr, const uint16
 //            CRLFCRLF, and "one ': ' per line" as an alternation check with a carry chain.
 // A group that does not qualify (unordered or overlapping messages, a span over kSpanMax) is
 // scanned message-per-lane by scan_lists, with identical results.
-#ifndef SHL_OPT_SPANMAX
-#define SHL_OPT_SPANMAX 20480         // bytes of span a warp keeps bitmaps for (config 2: 16.4 KiB +- 0.4)
-#endif
 constexpr uint32_t kSpanMax = SHL_OPT_SPANMAX;
 constexpr uint32_t kBmWords = kSpanMax / 32u + 2u;         // + the straddling word + one zero word behind the last
 static_assert(kBmWords * 8u >= (kCrCap * 32u + 2u + kSepCap * 32u + 2u) * 2u, "the per-lane lists share the bitmaps' storage");
@@ -435,6 +436,7 @@ __device__ __forceinline__ void group_bitmaps(const uint8_t* A0, const uint32_t 
         uint32_t c = __shfl_up_sync(SHL_FULL, vb.w, 1);
         if (lane == 0) c = prev_last;
         prev_last = __shfl_sync(SHL_FULL, vb.w, 31);
+        SHL_CHK(w < kBmWords);
         bm[w] = window_bits(c, va, vb);
         va = na; vb = nb;
 #if SHL_OPT_ROWS_AHEAD >= 2
@@ -492,6 +494,7 @@ __device__ __forceinline__ void put_record(const uint8_t* m, shl_hdr_span* out, 
     }
     const int klen = sep - ls;
     const uint32_t lo = (uint32_t)ls | ((uint32_t)klen << 16), hi = (uint32_t)vs | ((uint32_t)(ve - vs) << 16);
+    SHL_CHK(ls >= 0 && sep >= ls && end >= sep + 2 && end < 65536 && ve >= vs);
     *reinterpret_cast<uint2*>(out + k) = make_uint2(lo, hi);
     if (klen == 14) { if (!nc.n14) { nc.lo14 = lo; nc.hi14 = hi; } nc.n14++; }
     if (klen == 17) { if (!nc.n17) { nc.lo17 = lo; nc.hi17 = hi; } nc.n17++; }
