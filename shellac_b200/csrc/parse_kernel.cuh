@@ -446,6 +446,72 @@ __device__ __forceinline__ void group_bitmaps(const uint8_t* A0, const uint32_t 
     if (lane == 0) { bm2 z; z.x = z.y = 0u; bm[w] = z; }                        // the word behind the last row
 }
 
+// ----------------------------------------------------------------------------------- phase A, staged by TMA
+// Build option (SHL_OPT_TMA=1): the span's rows do not come through the warps' registers with LDG,
+// they are STAGED: one elected lane issues a bulk asynchronous copy (cp.async.bulk, the TMA unit;
+// UBLKCP in SASS) of each 1 KiB row into a small per-warp ring in shared memory and arms an
+// mbarrier with the byte count; the warp waits on the barrier's phase, every lane reads its 32
+// bytes with two LDS.128, and the slot is refilled kTmaSlots rows ahead.  Same bitmaps out.
+// Measured against the LDG path in profiles/r02/ (the ring costs shared memory, i.e. L1 and
+// resident warps; the LDG path with two rows in flight already hides the row latency).
+#ifndef SHL_OPT_TMA
+#define SHL_OPT_TMA 0
+#endif
+constexpr int kTmaSlots = 3;
+constexpr uint32_t kTmaRow = 1024u;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// global -> shared bulk copy (16-byte aligned, size a multiple of 16), completion counted on `bar`
+__device__ __forceinline__ void tma_row(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+// `it` is the warp's running row count (slot and barrier phase follow from it across groups)
+__device__ __forceinline__ void group_bitmaps_tma(const uint8_t* A0, const uint32_t nbytes, bm2* bm, const int lane,
+                                                  uint8_t* ring, uint64_t* bars, uint32_t& it) {
+    const uint32_t rows = (nbytes + kTmaRow - 1u) / kTmaRow;
+    auto issue = [&](uint32_t r) {
+        const uint32_t left = nbytes - r * kTmaRow;
+        const uint32_t bytes = min(kTmaRow, (left + 15u) & ~15u);      // past the span only inside the arena's padding
+        const uint32_t slot = (it + r) % kTmaSlots;
+        mbar_expect_tx(&bars[slot], bytes);
+        tma_row(ring + slot * kTmaRow, A0 + (size_t)r * kTmaRow, bytes, &bars[slot]);
+    };
+    if (lane == 0) for (uint32_t r = 0; r < rows && r < (uint32_t)kTmaSlots; r++) issue(r);
+    uint32_t prev_last = 0u, w = (uint32_t)lane;
+    for (uint32_t r = 0; r < rows; r++, w += 32u) {
+        const uint32_t slot = (it + r) % kTmaSlots, parity = ((it + r) / kTmaSlots) & 1u;
+        mbar_wait(&bars[slot], parity);
+        const uint4* t = reinterpret_cast<const uint4*>(ring + slot * kTmaRow + (uint32_t)lane * 32u);
+        const uint4 va = t[0], vb = t[1];
+        uint32_t c = __shfl_up_sync(SHL_FULL, vb.w, 1);
+        if (lane == 0) c = prev_last;
+        prev_last = __shfl_sync(SHL_FULL, vb.w, 31);
+        SHL_CHK(w < kBmWords);
+        bm[w] = window_bits(c, va, vb);
+        __syncwarp();                                                   // every lane has read the slot: it may be refilled
+        if (lane == 0 && r + (uint32_t)kTmaSlots < rows) issue(r + (uint32_t)kTmaSlots);
+    }
+    it += rows;
+    if (lane == 0) { bm2 z; z.x = z.y = 0u; bm[w] = z; }
+}
+
 // ----------------------------------------------------------------------------------- epilogue helpers
 // Canonical request line  METHOD SP URL SP "HTTP/1.x" CRLF  with a method of at most 7 bytes:
 // everything is decided from the line's first 8 and last 9 bytes (five independent loads, one
@@ -600,10 +666,21 @@ template <bool kPlace, bool kFull>     // kFull: 32 messages per warp (compile-t
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_route(const RouteArgs a) {
     __shared__ bm2 s_bm[kWarpsPerBlock][kBmWords];             // the group's bitmaps; the per-lane path keeps its lists here
     __shared__ uint32_t s_codes[64];
+#if SHL_OPT_TMA
+    __shared__ __align__(128) uint8_t s_ring[kWarpsPerBlock][kTmaSlots * kTmaRow];
+    __shared__ __align__(8) uint64_t s_bar[kWarpsPerBlock][kTmaSlots];
+    uint32_t tma_it = 0u;
+#endif
     extern __shared__ uint32_t s_hist[];                       // kPlace: n_hosts bins (when they fit)
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const SwarK K = a.k;
+#if SHL_OPT_TMA
+    if (lane == 0) {
+        for (int k = 0; k < kTmaSlots; k++) mbar_init(&s_bar[warp][k], 1u);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+#endif
     if (threadIdx.x < 64) s_codes[threadIdx.x] = 0u;
     const bool smem_hist = kPlace && a.place.hist != nullptr && a.n_hosts <= 4096u;
     if (smem_hist) for (uint32_t i = threadIdx.x; i < a.n_hosts; i += blockDim.x) s_hist[i] = 0u;
@@ -641,7 +718,11 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
             const bool ok = !have || ((lane == 0 || m >= prev_end) && (uint64_t)(my_end - A0) <= (uint64_t)kSpanMax);
             if (__all_sync(SHL_FULL, ok)) {
                 const uint32_t nbytes = __reduce_max_sync(SHL_FULL, have ? (uint32_t)(my_end - A0) : 0u);
+#if SHL_OPT_TMA
+                group_bitmaps_tma(A0, nbytes, s_bm[warp], lane, s_ring[warp], s_bar[warp], tma_it);
+#else
                 group_bitmaps(A0, nbytes, s_bm[warp], lane);
+#endif
                 __syncwarp();
                 coal = true;
                 s0 = (uint32_t)(m - A0);
