@@ -145,6 +145,22 @@ typedef struct shl_body_out {
     uint64_t* body_used;       /* one element                                                      */
 } shl_body_out;
 
+/* Compact per-message record (32 bytes, one memory sector): everything shl_parse_out + the node of
+ * shl_place_out say about a message, for callers that bring results back over PCIe (72 bytes per
+ * request become 32; the MD5 is optional and the hash, its first four bytes, is dropped).
+ * Offsets are relative to the message and fit 16 bits by the library's 64 KiB header limit; a first
+ * line that does not (no CRLF within 64 KiB) is SHL_E_LIB_HDR_TOO_LARGE here.  `tail`: requests
+ * carry their node (0xffff = not placed; rings of at most 65 534 nodes), responses their status
+ * code (SHL_F_STATUS_WIDE when it does not fit 16 bits: the host converts the span).            */
+typedef struct shl_msg_rec {
+    uint32_t status;
+    uint32_t hdr_base;
+    int64_t  content_len;
+    uint16_t first_line_len, headers_len, sp1, sp2, fl_end, slash;
+    uint16_t n_headers;
+    uint16_t tail;
+} shl_msg_rec;
+
 /* Placement result (struct-of-arrays, n elements each). */
 typedef struct shl_place_out {
     uint8_t*  md5;             /* 16 bytes per key: RFC 1321 digest (libhashkit md5.c)              */
@@ -222,6 +238,16 @@ int  shl_place_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes,
 int  shl_route_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes,
                      const uint64_t* off, const uint32_t* len, uint64_t n,
                      const shl_parse_out* pout, const shl_place_out* qout);
+/* shl_route_batch with the compact record as its output: rec[n], the header records, and optionally
+ * the digests (md5 may be NULL) and the per-node histogram (hist may be NULL; ADDED to).  Same kernel,
+ * same H2D / kernel / D2H pipelining; 32 + 8 x n_headers bytes come back per request.             */
+int  shl_route_compact_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes,
+                             const uint64_t* off, const uint32_t* len, uint64_t n,
+                             shl_msg_rec* rec, shl_hdr_span* hdr, uint64_t hdr_cap, uint64_t* hdr_used,
+                             uint8_t* md5, uint64_t* hist);
+int  shl_route_compact_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_off, const uint32_t* d_len,
+                           uint64_t n, shl_msg_rec* d_rec, shl_hdr_span* d_hdr, uint64_t hdr_cap,
+                           uint64_t* d_hdr_used, uint8_t* d_md5, uint64_t* d_hist);
 /* One CHUNK_HEADER_RX.match + _parse_chunk_size at the START of each window (HttpParser.py:253-261):
  * hdr_len[i] = len(match.group()) or -1 when the regex does not match; size[i] = int(size, 16);
  * ok[i] = 0 when that int() raises ValueError.  The primitive an incremental caller needs.       */

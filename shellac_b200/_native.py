@@ -45,6 +45,9 @@ CODE_EXC = {16: ValueError, 17: ValueError, 18: ValueError, 19: ValueError, 20: 
             32: OverflowError, 33: MemoryError}
 
 HDR_DTYPE = np.dtype([('key_off', '<u2'), ('key_len', '<u2'), ('val_off', '<u2'), ('val_len', '<u2')])
+REC_DTYPE = np.dtype([('status', '<u4'), ('hdr_base', '<u4'), ('content_len', '<i8'), ('first_line_len', '<u2'),
+                      ('headers_len', '<u2'), ('sp1', '<u2'), ('sp2', '<u2'), ('fl_end', '<u2'), ('slash', '<u2'),
+                      ('n_headers', '<u2'), ('tail', '<u2')])      # shl_msg_rec
 CHUNK_DTYPE = np.dtype([('hdr_off', '<u4'), ('hdr_len', '<u4'), ('data_off', '<u4'), ('data_len', '<u4')])
 
 _u8p, _u32p, _i32p = C.POINTER(C.c_uint8), C.POINTER(C.c_uint32), C.POINTER(C.c_int32)
@@ -141,6 +144,8 @@ def lib():
         'shl_frame_dev': (i32, [vp, vp, vp, vp, u64, vp, vp, vp, C.POINTER(FrameOutStruct)]),
         'shl_place_dev': (i32, [vp, vp, vp, vp, u64, C.POINTER(PlaceOutStruct)]),
         'shl_route_dev': (i32, [vp, vp, vp, vp, u64, C.POINTER(ParseOutStruct), C.POINTER(PlaceOutStruct)]),
+        'shl_route_compact_batch': (i32, [vp, vp, u64, vp, vp, u64, vp, vp, u64, vp, vp, vp]),
+        'shl_route_compact_dev': (i32, [vp, vp, vp, vp, u64, vp, vp, u64, vp, vp, vp]),
         'shl_place_static': (i32, [i32, vp, u64, vp, vp, u64, vp, vp, C.c_uint32, C.c_uint32, vp, vp, vp, vp]),
         'shl_launch_count': (u64, [vp]),
         'shl_code_hist': (i32, [vp, vp, i32]),

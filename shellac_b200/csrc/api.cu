@@ -59,6 +59,7 @@ struct shl_ctx {
     ncclComm_t comm = nullptr; int comm_rank = 0, comm_world = 1;
     uint64_t* d_scratch = nullptr; uint64_t* h_scratch = nullptr;             // 64 words for shl_comm_allreduce_u64
     uint64_t cur_n = 0;                   // messages of the last *_batch parse (frame_batch checks it)
+    shl_msg_rec* d_crec = nullptr;        // compact records (lazy)
     uint64_t* d_mc_off = nullptr; uint64_t* d_mc_sums = nullptr; uint8_t* d_mc_frames = nullptr; uint32_t* d_mc_vlen = nullptr;   // memcached frames (lazy)
     uint64_t mc_frames_cap = 0;
     uint8_t* d_lkeys = nullptr; uint32_t* d_lkey_base = nullptr;   // lower-cased header names (lazy; d_counters[2] counts the bytes)
@@ -320,7 +321,7 @@ void shl_ctx_destroy(shl_ctx* ctx) {
     for (auto& e : ctx->ev_stats_done) if (e) cudaEventDestroy(e);
     cudaFree(ctx->d_ring_values); cudaFree(ctx->d_ring_nodes); cudaFree(ctx->d_ring_dir); cudaFree(ctx->d_hist);
     cudaFree(ctx->d_body); cudaFree(ctx->d_body_off); cudaFree(ctx->d_body_len);
-    cudaFree(ctx->d_lkeys); cudaFree(ctx->d_lkey_base);
+    cudaFree(ctx->d_lkeys); cudaFree(ctx->d_lkey_base); cudaFree(ctx->d_crec);
     cudaFree(ctx->d_mc_off); cudaFree(ctx->d_mc_sums); cudaFree(ctx->d_mc_frames); cudaFree(ctx->d_mc_vlen);
     cudaFree(ctx->d_gstart); cudaFree(ctx->d_gcursor); cudaFree(ctx->d_gorder);
     for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
@@ -476,7 +477,8 @@ static int check_arena(shl_ctx* ctx, const void* arena) {
 }
 
 static int launch_route(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_off, const uint32_t* d_len, uint64_t n,
-                        const shl_parse_out* d_out, const shl_place_out* d_q, cudaStream_t stream = nullptr, uint32_t bias = 0) {
+                        const shl_parse_out* d_out, const shl_place_out* d_q, cudaStream_t stream = nullptr, uint32_t bias = 0,
+                        shl_msg_rec* d_crec = nullptr) {
     if (!stream && ctx) stream = ctx->stream;
     if (!ctx || !d_arena || !d_off || !d_len || !d_out) return fail(ctx, SHL_ERR_ARG, "null pointer");
     CU(cudaSetDevice(ctx->device));
@@ -488,6 +490,7 @@ static int launch_route(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_
     a.code_hist = cur_codes(ctx); a.force_scalar = ctx->force_scalar;
     a.k = shl::swar_host_consts();
     a.hdr_base_bias = bias;
+    a.crec = d_crec;
     // a warp takes 32 messages when there are enough of them to fill the machine; a reactor-sized
     // batch is spread over more warps (down to one message each) so that the kernel's critical
     // path is one message's worth of rows, not thirty-two
@@ -696,7 +699,7 @@ static int route_small(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes,
 // biased so they index the caller's arena directly.  Returns 1 when the batch is not chunkable
 // (offsets not locally dense) so the caller falls back to the single-stream path.
 static int route_pipelined(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, const uint64_t* off, const uint32_t* len,
-                           uint64_t n, const shl_parse_out* pout, const shl_place_out* qout) {
+                           uint64_t n, const shl_parse_out* pout, const shl_place_out* qout, shl_msg_rec* crec = nullptr) {
     constexpr int kPipe = shl_ctx::kPipe, kMaxChunks = shl_ctx::kMaxChunks;
     if (!ctx->pipeline || !arena || n < 65536) return 1;
     ctx->cur_dp = ctx->dp; ctx->cur_n = n;
@@ -716,6 +719,10 @@ static int route_pipelined(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_by
     if (cap_c == 0 || cap_c * nch > 0xffffffffull) return 1;
     CU(cudaMemsetAsync(ctx->d_chunk_used, 0, kMaxChunks * 8, ctx->stream));
     shl_place_out dq = ctx->dq;
+    if (crec) {               // compact output: the record carries the node; digests only if asked for
+        dq.hash = nullptr; dq.node = nullptr; dq.md5 = qout->md5 ? ctx->dq.md5 : nullptr;
+        ctx->cur_node = nullptr;
+    }
     if (qout) {
         dq.hist = qout->hist ? ctx->d_hist : nullptr;
         if (dq.hist) CU(cudaMemsetAsync(ctx->d_hist, 0, (size_t)ctx->n_hosts * 8, ctx->stream));
@@ -740,9 +747,10 @@ static int route_pipelined(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_by
         o.status_code += i0; o.n_headers += i0; o.hdr_base += i0; o.content_len += i0;
         o.hdr = d.hdr + (uint64_t)c * cap_c; o.hdr_cap = cap_c; o.hdr_used = ctx->d_chunk_used + c;
         shl_place_out q = dq;
-        if (qout) { q.md5 += 16 * i0; q.hash += i0; q.node += i0; }
+        if (qout) { if (q.md5) q.md5 += 16 * i0; if (q.hash) q.hash += i0; if (q.node) q.node += i0; }
         if (int rc = launch_route(ctx, ctx->d_arena, ctx->d_off + i0, ctx->d_len + i0, m, &o, qout ? &q : nullptr, st,
-                                  (uint32_t)((uint64_t)c * cap_c))) return rc;
+                                  (uint32_t)((uint64_t)c * cap_c), crec ? ctx->d_crec + i0 : nullptr)) return rc;
+        if (crec) CU(cudaMemcpyAsync(crec + i0, ctx->d_crec + i0, m * sizeof(shl_msg_rec), cudaMemcpyDeviceToHost, st));
         D2S(pout->status, d.status, m, 4); D2S(pout->first_line_len, d.first_line_len, m, 4); D2S(pout->headers_len, d.headers_len, m, 4);
         D2S(pout->sp1, d.sp1, m, 4); D2S(pout->sp2, d.sp2, m, 4); D2S(pout->fl_end, d.fl_end, m, 4); D2S(pout->slash, d.slash, m, 4);
         D2S(pout->status_code, d.status_code, m, 4); D2S(pout->n_headers, d.n_headers, m, 4); D2S(pout->hdr_base, d.hdr_base, m, 4);
@@ -844,6 +852,46 @@ int shl_route_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, co
     if (int rc = parse_out_d2h(ctx, pout, n)) return rc;
     if (int rc = lkeys_d2h(ctx, pout, n)) return rc;
     return place_out_d2h(ctx, qout, n);
+}
+
+// ---- compact output: one 32-byte record per message
+int shl_route_compact_dev(shl_ctx* ctx, const uint8_t* d_arena, const uint64_t* d_off, const uint32_t* d_len, uint64_t n,
+                          shl_msg_rec* d_rec, shl_hdr_span* d_hdr, uint64_t hdr_cap, uint64_t* d_hdr_used, uint8_t* d_md5, uint64_t* d_hist) {
+    if (!ctx || !d_rec || !d_hdr || !d_hdr_used) return fail(ctx, SHL_ERR_ARG, "shl_route_compact_dev: null pointer");
+    if (ctx->n_hosts > 65534u) return fail(ctx, SHL_ERR_ARG, "compact records hold the node in 16 bits: rings of at most 65 534 nodes");
+    shl_parse_out o{};
+    o.hdr = d_hdr; o.hdr_cap = hdr_cap; o.hdr_used = d_hdr_used;
+    shl_place_out q{};
+    q.md5 = d_md5; q.hist = d_hist;
+    return launch_route(ctx, d_arena, d_off, d_len, n, &o, &q, nullptr, 0, d_rec);
+}
+
+int shl_route_compact_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, const uint64_t* off, const uint32_t* len,
+                            uint64_t n, shl_msg_rec* rec, shl_hdr_span* hdr, uint64_t hdr_cap, uint64_t* hdr_used,
+                            uint8_t* md5, uint64_t* hist) {
+    if (!ctx || !rec || !off || !len) return fail(ctx, SHL_ERR_ARG, "shl_route_compact_batch: null pointer");
+    if (!ctx->d_ring_values) return fail(ctx, SHL_ERR_NO_RING, "shl_ring_build() has not been called");
+    if (ctx->n_hosts > 65534u) return fail(ctx, SHL_ERR_ARG, "compact records hold the node in 16 bits: rings of at most 65 534 nodes");
+    if (n > ctx->max_msgs || arena_bytes > ctx->max_bytes) return fail(ctx, SHL_ERR_ARG, "batch larger than the capacity given to shl_ctx_create");
+    CU(cudaSetDevice(ctx->device));
+    if (!ctx->d_crec) CU(dalloc(&ctx->d_crec, ctx->max_msgs));
+    shl_parse_out pout{};
+    pout.hdr = hdr; pout.hdr_cap = hdr_cap; pout.hdr_used = hdr_used;
+    shl_place_out qout{};
+    qout.md5 = md5; qout.hist = hist;
+    int rc = route_pipelined(ctx, arena, arena_bytes, off, len, n, &pout, &qout, rec);
+    if (rc <= 0) return rc;
+    if (int rc2 = stage_in(ctx, arena, arena_bytes, off, len, n, ctx->d_off, ctx->d_len)) return rc2;
+    CU(cudaMemsetAsync(ctx->d_counters, 0, 8, ctx->stream));
+    shl_place_out dq = ctx->dq;
+    dq.hist = hist ? ctx->d_hist : nullptr;
+    dq.md5 = md5 ? ctx->dq.md5 : nullptr; dq.hash = nullptr; dq.node = nullptr;
+    if (dq.hist) CU(cudaMemsetAsync(ctx->d_hist, 0, (size_t)ctx->n_hosts * 8, ctx->stream));
+    ctx->cur_node = nullptr; ctx->cur_hist = dq.hist;
+    if (int rc2 = launch_route(ctx, ctx->d_arena, ctx->d_off, ctx->d_len, n, &ctx->dp, &dq, nullptr, 0, ctx->d_crec)) return rc2;
+    CU(cudaMemcpyAsync(rec, ctx->d_crec, n * sizeof(shl_msg_rec), cudaMemcpyDeviceToHost, ctx->stream));
+    if (int rc2 = parse_out_d2h(ctx, &pout, n)) return rc2;
+    return place_out_d2h(ctx, &qout, n);
 }
 
 int shl_place_batch(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_bytes, const uint64_t* key_off, const uint32_t* key_len,

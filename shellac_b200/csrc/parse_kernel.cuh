@@ -93,6 +93,7 @@ struct RouteArgs {
     int force_scalar;                 // test hook: take the scalar path for every message
     SwarK k;                          // SWAR byte constants, as run-time values (see SwarK)
     uint32_t hdr_base_bias;           // added to the stored hdr_base (out.hdr may be a slice of a larger arena)
+    shl_msg_rec* crec;                // != null: compact output, one 32-byte record per message instead of the arrays of `out`
     uint32_t group;                   // messages per warp, 1..32 (small batches: fewer per warp, more warps, shorter chains)
     // fused placement (route); ring_values == nullptr -> parse only
     const uint32_t* ring_values; const uint32_t* ring_nodes; const uint32_t* ring_dir; uint32_t n_points, n_hosts;
@@ -410,12 +411,23 @@ __device__ __forceinline__ bm2 window_bits(const uint32_t c, const uint4& va, co
 }
 
 // bitmaps of span[0:nbytes) (A0 is 32-byte aligned, nbytes <= kSpanMax)
+#ifndef SHL_OPT_ROWS_NOALLOC
+#define SHL_OPT_ROWS_NOALLOC 0
+#endif
 #ifndef SHL_OPT_ROWS_AHEAD
 #define SHL_OPT_ROWS_AHEAD 2          // rows of the span in flight ahead of the one being classified
 #endif
 __device__ __forceinline__ void row_load(const uint8_t* A0, const uint32_t off, const uint32_t nbytes, uint4& a, uint4& b) {
     a = b = make_uint4(0u, 0u, 0u, 0u);
-    if (off < nbytes) { a = __ldg(reinterpret_cast<const uint4*>(A0 + off)); b = __ldg(reinterpret_cast<const uint4*>(A0 + off + 16)); }
+    if (off < nbytes) {
+#if SHL_OPT_ROWS_NOALLOC
+        // the span streams through once: keep it out of L1, which the epilogue's first-line / URL / value-edge reads need
+        asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w) : "l"(A0 + off));
+        asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w) : "l"(A0 + off + 16));
+#else
+        a = __ldg(reinterpret_cast<const uint4*>(A0 + off)); b = __ldg(reinterpret_cast<const uint4*>(A0 + off + 16));
+#endif
+    }
 }
 __device__ __forceinline__ void group_bitmaps(const uint8_t* A0, const uint32_t nbytes, bm2* bm, const int lane) {
     uint32_t prev_last = 0u;
@@ -869,7 +881,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
             r.sp2 - r.sp1 - 1u > (uint32_t)SHL_MAX_KEY_LEN) r.status |= SHL_F_KEY_TOO_LONG;      // pylibmc raises before hashing (Server.py:335)
 
         // ---- per-message fixed fields: lane j == message j, so these are coalesced SoA stores
-        if (have) {
+        if (have && a.crec == nullptr) {
             a.out.status[mine] = r.status;
             a.out.first_line_len[mine] = r.first_line_len;
             a.out.headers_len[mine] = r.headers_len;
@@ -879,10 +891,18 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
             a.out.n_headers[mine] = r.n_headers;
             a.out.hdr_base[mine] = (uint32_t)my_base + a.hdr_base_bias;
             a.out.content_len[mine] = r.content_len;
-            atomicAdd(&s_codes[r.status & 63u], 1u);
         }
+        if (have && a.crec != nullptr && (r.first_line_len > 65535u || (r.status & (SHL_F_STATUS_WIDE)) ||
+                                          (!(r.status & SHL_F_IS_REQUEST) && (uint32_t)r.status_code > 65535u))) {
+            // the compact record keeps these in 16 bits: a first line beyond 64 KiB is a library limit
+            // there, a status code beyond 16 bits is handed to the host like any other wide one
+            if (r.first_line_len > 65535u) { r.status = (r.status & ~0xffu) | SHL_E_LIB_HDR_TOO_LARGE; r.first_line_len = 0; }
+            else r.status |= SHL_F_STATUS_WIDE;
+        }
+        if (have) atomicAdd(&s_codes[r.status & 63u], 1u);
 
         // ---- fused key + MD5 + ketama: the URL is the key, verbatim  (Server.py:325-335)
+        uint32_t rec_node = 0xffffffffu;
         if (kPlace && have) {
             const bool routable = (r.status & SHL_F_MESSAGE_COMPLETE) && (r.status & SHL_F_IS_REQUEST) &&
                                   (r.status & SHL_F_FIRST_LINE_DONE) && (r.status & 0xffu) == SHL_S_OK &&
@@ -906,6 +926,18 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
             }
             if (a.place.hash) a.place.hash[mine] = hash0;
             if (a.place.node) a.place.node[mine] = node;
+            rec_node = node;
+        }
+        // ---- compact output: ONE 32-byte record per message (two 16-byte stores, a whole sector)
+        if (have && a.crec != nullptr) {
+            const uint32_t tail = (r.status & SHL_F_IS_REQUEST) ? min(rec_node, 0xffffu) : ((uint32_t)r.status_code & 0xffffu);
+            uint4 lo, hi;
+            lo.x = r.status; lo.y = (uint32_t)my_base + a.hdr_base_bias;
+            lo.z = (uint32_t)(uint64_t)r.content_len; lo.w = (uint32_t)((uint64_t)r.content_len >> 32);
+            hi.x = r.first_line_len | (r.headers_len << 16); hi.y = r.sp1 | (r.sp2 << 16);
+            hi.z = r.fl_end | (r.slash << 16); hi.w = r.n_headers | (tail << 16);
+            uint4* dst = reinterpret_cast<uint4*>(a.crec + mine);
+            dst[0] = lo; dst[1] = hi;
         }
     }
     __syncthreads();

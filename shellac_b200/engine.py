@@ -147,6 +147,23 @@ class Engine(object):
             self.sync()
         return pout, qout
 
+    def route_compact(self, arena, hdr_cap=0, want_md5=False, sync=True, out=None):
+        """shl_route_compact_batch: (rec[n] of N.REC_DTYPE, hdr records, hdr_used, md5 or None, hist).
+        `out` = the tuple a previous call returned (the pinned arrays are reused)."""
+        n = arena.n
+        cap = self._hdr_cap(arena, hdr_cap)
+        if out is None:
+            out = (self.pinned(n, N.REC_DTYPE), self.pinned(cap, N.HDR_DTYPE), self.pinned(1, np.uint64),
+                   self.pinned(16 * n, np.uint8) if want_md5 else None, self.pinned(max(self.n_hosts, 1), np.uint64))
+        rec, hdr, used, md5, hist = out
+        rc = self.lib.shl_route_compact_batch(self.ctx, arena.data.ctypes.data, arena.nbytes, arena.off.ctypes.data,
+                                              arena.len.ctypes.data, n, rec.ctypes.data, hdr.ctypes.data, len(hdr), used.ctypes.data,
+                                              md5.ctypes.data if md5 is not None else None, hist.ctypes.data)
+        _check(self.lib, self.ctx, rc, 'shl_route_compact_batch')
+        if sync:
+            self.sync()
+        return out
+
     def place(self, arena, key_off=None, key_len=None, sync=True, out=None):
         key_off = arena.off if key_off is None else key_off
         key_len = arena.len if key_len is None else key_len

@@ -700,3 +700,37 @@ def test_memcached_frames_per_node(eng, golden):
         i = int(order[j])
         key = ar.message(i)[int(pg.sp1[i]) + 1:int(pg.sp2[i])]
         assert blob[int(foff[j]):int(foff[j + 1])] == py_port.mc_set_header(key, i, int(vlen[i]), 170), j
+
+
+def test_compact_records_equal_the_wide_layout(eng, golden):
+    """shl_route_compact_batch: the 32-byte record per message says what the struct-of-arrays fields and
+    the node of shl_route_batch say (small batch and the chunked large-batch path)."""
+    hosts = ['10.0.0.%d' % (i + 1) for i in range(16)]
+    eng.ring_build(hosts)
+    c2 = eng.corpus_host(20130725, 50000, 70000, 0)
+    for msgs in ([w['msg'] for w in golden['whole']], [c2.message(i) for i in range(70000)] + [w['msg'] for w in golden['whole'][:500]]):
+        ar = eng.pack(msgs)
+        n = ar.n
+        pg, qg = eng.route(ar)
+        rec, hdr, used, md5, hist = eng.route_compact(ar, want_md5=True)
+        rec = rec[:n]
+        wide_first = pg.first_line_len[:n] > 65535
+        st = pg.status[:n].copy()
+        assert not wide_first.any()
+        sc = pg.status_code[:n].astype(np.int64)
+        resp_wide = ((st & N.F_IS_REQUEST) == 0) & ((sc > 65535) | (sc < 0))
+        st[resp_wide] |= N.F_STATUS_WIDE
+        assert (rec['status'] == st).all()
+        for f in ('first_line_len', 'headers_len', 'sp1', 'sp2', 'fl_end', 'slash', 'n_headers', 'content_len'):
+            assert (rec[f].astype(np.int64) == getattr(pg, f)[:n].astype(np.int64)).all(), f
+        req = (st & N.F_IS_REQUEST) != 0
+        assert (rec['tail'][req] == np.minimum(qg.node[:n][req], 0xffff)).all()
+        ok_resp = ~req & ((st & N.F_STATUS_WIDE) == 0)
+        assert (rec['tail'][ok_resp] == (pg.status_code[:n][ok_resp].astype(np.int64) & 0xffff)).all()
+        assert (md5[:16 * n] == qg.md5[:16 * n]).all() and hist[:16].tolist() == qg.hist.tolist()
+        assert int(used[0]) == int(pg.hdr_used[0])
+        # same header records behind hdr_base
+        a = _records(pg, n)
+        class R: pass
+        r = R(); r.n_headers, r.hdr_base, r.hdr = rec['n_headers'].astype(np.uint32), rec['hdr_base'], hdr
+        assert (_records(r, n) == a).all()
