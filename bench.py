@@ -401,9 +401,12 @@ class Job(object):
     def sum_over_ranks(self, x):
         return int(self.eng.allreduce_u64([int(x)], op='sum')[0])
 
-    def timed(self, fn, steps, warmup, flush=None):
+    def timed(self, fn, steps, warmup, flush=None, regions=1):
         """W untimed steps, then exactly K steps between two barriers, timed with CUDA events on the
-        ctx stream; returns (ms = max over ranks, clocks, kernel launches)."""
+        ctx stream; returns (ms = max over ranks, clocks, kernel launches).  regions > 1 repeats the
+        timed region (K steps each, its own barriers) and reports the MEDIAN region, so that a
+        millisecond-long region is not at the mercy of one hiccup and the clock sampler sees more
+        than a handful of samples; self.region_ms keeps every region's time."""
         eng = self.eng
         for i in range(warmup):
             fn(i)
@@ -411,19 +414,23 @@ class Job(object):
             flush()
         sampler = ClockSampler(self.local)
         sampler.start()
-        self.barrier()
-        sampler.armed.set()
-        l0 = eng.launches()
-        eng.event(0)
-        for i in range(steps):
-            fn(i)
-        if flush:
-            flush()
-        eng.event(1)
-        self.barrier()
-        ms = eng.elapsed_ms(0, 1)
+        times, launches = [], 0
+        for _ in range(regions):
+            self.barrier()
+            sampler.armed.set()
+            l0 = eng.launches()
+            eng.event(0)
+            for i in range(steps):
+                fn(i)
+            if flush:
+                flush()
+            eng.event(1)
+            self.barrier()
+            times.append(self.max_over_ranks(eng.elapsed_ms(0, 1)))
+            launches = eng.launches() - l0
         clocks = sampler.result()
-        return self.max_over_ranks(ms), clocks, eng.launches() - l0
+        self.region_ms = times
+        return float(np.median(times)), clocks, launches
 
     def pcie_probe(self, d_buf, h_buf, nbytes):
         """Pinned copies of the step's bytes: each direction alone, then both at once on two streams,
@@ -522,8 +529,10 @@ def run_route(args):
         step(i)
     flush()
     st['units'] = 0
-    ms, clocks, launches = job.timed(step, steps, 0, flush)
-    units = job.sum_over_ranks(st['units'])
+    regions = 5 if cfg == 2 else 1
+    ms, clocks, launches = job.timed(step, steps, 0, flush, regions=regions)
+    region_ms = list(job.region_ms)
+    units = job.sum_over_ranks(st['units']) // regions
 
     # kernel-only duration for the roofline: events around the kernel alone
     eng.sync()
@@ -613,6 +622,7 @@ def run_route(args):
         'mean_request_bytes': b0_bytes / m0, 'mean_header_lines': n_hdr / m0,
         'header_gb_s': value * b0_bytes / m0 / 1e9,
         'clocks': clocks, 'gpu_launches': launches, 'check': check,
+        'timed_regions': {'count': regions, 'ms_each': region_ms, 'reported': 'median region; every region is exactly K steps between two barriers'},
         'e2e': {'value': e2e_c, 'unit': unit, 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': ar.n * 32 + e_hdr * 8 + nh * 8 + 8,
                 'header_gb_s': nbytes * world * e_steps / (c_ms / 1e3) / 1e9, 'steps': e_steps,
                 'pcie_gb_s_h2d': h2d * e_steps / (c_ms / 1e3) / 1e9, 'ms_per_step': c_ms / e_steps,

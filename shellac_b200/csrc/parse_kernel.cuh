@@ -42,7 +42,10 @@ namespace shl {
 #ifndef SHL_OPT_BATCH
 #define SHL_OPT_BATCH 2               // header lines whose value peeks are in flight together
 #endif
-constexpr int kWarpsPerBlock = 4;
+#ifndef SHL_OPT_WARPS
+#define SHL_OPT_WARPS 4
+#endif
+constexpr int kWarpsPerBlock = SHL_OPT_WARPS;
 constexpr int kGroup = 32;            // messages per warp (one per lane)
 constexpr int kCrCap = 24;            // CRLF positions a lane can list (first line + 23 header lines)
 constexpr int kSepCap = 28;           // ": " positions a lane can list
