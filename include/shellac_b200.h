@@ -361,7 +361,7 @@ void* shl_node_hist_dev(shl_ctx* ctx);   /* uint64_t[n_hosts], filled by *_batch
  * Counters across GPUs.  The path shards by request batch, one process per GPU, with no exchange
  * of payloads; the ranks of a job only sum their COUNTERS: uint64[n_hosts + SHL_N_CODES], the
  * per-node placement histogram followed by the per-outcome counts (there is
- * no counterpart in the reference, which is one single-threaded process).  The library owns two
+ * no counterpart in the reference, which is one single-threaded process).  The library owns four
  * such device buffers, the NCCL communicator and a side stream.
  *   shl_stats_dev      the CURRENT buffer: hand it to a *_dev call as place.hist so the kernel adds
  *                      its histogram there; the outcome counts of every parse/route call land
@@ -372,7 +372,7 @@ void* shl_node_hist_dev(shl_ctx* ctx);   /* uint64_t[n_hosts], filled by *_batch
  *                      Without a communicator everything below still works, on one rank's counters.
  *   shl_stats_allreduce  closes the current buffer: summed over the ranks (ncclAllReduce, uint64,
  *                      sum) on the side stream, ordered after everything queued on the ctx stream,
- *                      result also copied to pinned host memory; the other buffer, zeroed, becomes
+ *                      result also copied to pinned host memory; the next buffer, zeroed, becomes
  *                      current.  Returns at once: the kernel of the next batch overlaps the reduce.
  *   shl_stats_join     makes the ctx STREAM wait for the outstanding reduces (call it before
  *                      recording the event that ends a timed region).

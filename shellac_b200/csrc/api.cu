@@ -52,10 +52,11 @@ struct shl_ctx {
     uint8_t* d_body = nullptr; uint64_t* d_body_off = nullptr; uint64_t* d_body_len = nullptr;   // body gather (lazy)
     // counters shared between GPUs: [placement histogram n_hosts | outcome codes 64], two buffers so
     // that the all-reduce of batch k (comm stream) overlaps the kernel of batch k + 1 (ctx stream)
-    uint64_t* d_stats[2] = {nullptr, nullptr}; uint64_t* h_stats = nullptr;   // h_stats: pinned, 2 x stats_len
+    static constexpr int kStatBufs = 4;   // a buffer is reused four batches later: the ranks of a job need not run in lock-step
+    uint64_t* d_stats[kStatBufs] = {}; uint64_t* h_stats = nullptr;   // h_stats: pinned, kStatBufs x stats_len
     uint32_t stats_len = 0; int stat_k = 0, stat_last = -1;
     cudaStream_t comm_stream = nullptr;
-    cudaEvent_t ev_stats_ready[2]{}, ev_stats_done[2]{};
+    cudaEvent_t ev_stats_ready[kStatBufs]{}, ev_stats_done[kStatBufs]{};
     ncclComm_t comm = nullptr; int comm_rank = 0, comm_world = 1;
     uint64_t* d_scratch = nullptr; uint64_t* h_scratch = nullptr;             // 64 words for shl_comm_allreduce_u64
     uint64_t cur_n = 0;                   // messages of the last *_batch parse (frame_batch checks it)
@@ -223,11 +224,11 @@ const char* shl_last_error(shl_ctx* ctx) { return ctx ? ctx->err.c_str() : g_las
 
 static int stats_alloc(shl_ctx* ctx, uint32_t n_hosts) {
     const uint32_t len = n_hosts + SHL_N_CODES;
-    for (int k = 0; k < 2; k++) { cudaFree(ctx->d_stats[k]); ctx->d_stats[k] = nullptr; }
+    for (int k = 0; k < shl_ctx::kStatBufs; k++) { cudaFree(ctx->d_stats[k]); ctx->d_stats[k] = nullptr; }
     if (ctx->h_stats) { cudaFreeHost(ctx->h_stats); ctx->h_stats = nullptr; }
-    for (int k = 0; k < 2; k++) { CU(dalloc(&ctx->d_stats[k], len)); CU(cudaMemset(ctx->d_stats[k], 0, (size_t)len * 8)); }
-    CU(cudaHostAlloc(reinterpret_cast<void**>(&ctx->h_stats), 2 * (size_t)len * 8, cudaHostAllocDefault));
-    memset(ctx->h_stats, 0, 2 * (size_t)len * 8);
+    for (int k = 0; k < shl_ctx::kStatBufs; k++) { CU(dalloc(&ctx->d_stats[k], len)); CU(cudaMemset(ctx->d_stats[k], 0, (size_t)len * 8)); }
+    CU(cudaHostAlloc(reinterpret_cast<void**>(&ctx->h_stats), shl_ctx::kStatBufs * (size_t)len * 8, cudaHostAllocDefault));
+    memset(ctx->h_stats, 0, shl_ctx::kStatBufs * (size_t)len * 8);
     ctx->stats_len = len; ctx->stat_k = 0; ctx->stat_last = -1;
     return SHL_OK;
 }
@@ -313,7 +314,7 @@ void shl_ctx_destroy(shl_ctx* ctx) {
     if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
     cudaFree(ctx->d_counters);
     if (ctx->comm) g_nccl.CommDestroy(ctx->comm);
-    for (int k = 0; k < 2; k++) cudaFree(ctx->d_stats[k]);
+    for (int k = 0; k < shl_ctx::kStatBufs; k++) cudaFree(ctx->d_stats[k]);
     if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
     cudaFree(ctx->d_scratch); if (ctx->h_scratch) cudaFreeHost(ctx->h_scratch);
     if (ctx->comm_stream) { cudaStreamSynchronize(ctx->comm_stream); cudaStreamDestroy(ctx->comm_stream); }
@@ -1136,7 +1137,7 @@ int shl_comm_size(shl_ctx* ctx) { return ctx && ctx->comm ? ctx->comm_world : 1;
 int shl_stats_allreduce(shl_ctx* ctx) {
     if (!ctx) return SHL_ERR_ARG;
     CU(cudaSetDevice(ctx->device));
-    const int k = ctx->stat_k, k2 = k ^ 1;
+    const int k = ctx->stat_k, k2 = (k + 1) % shl_ctx::kStatBufs;
     const size_t bytes = (size_t)ctx->stats_len * 8;
     CU(cudaEventRecord(ctx->ev_stats_ready[k], ctx->stream));
     CU(cudaStreamWaitEvent(ctx->comm_stream, ctx->ev_stats_ready[k], 0));
@@ -1147,7 +1148,7 @@ int shl_stats_allreduce(shl_ctx* ctx) {
     CU(cudaMemcpyAsync(ctx->h_stats + (size_t)k * ctx->stats_len, ctx->d_stats[k], bytes, cudaMemcpyDeviceToHost, ctx->comm_stream));
     CU(cudaEventRecord(ctx->ev_stats_done[k], ctx->comm_stream));
     ctx->stat_last = k;
-    // the other buffer takes the next batches; its previous all-reduce (two calls ago) must be over
+    // the next buffer takes the next batches; its previous all-reduce (kStatBufs calls ago) must be over
     CU(cudaStreamWaitEvent(ctx->stream, ctx->ev_stats_done[k2], 0));
     CU(cudaMemsetAsync(ctx->d_stats[k2], 0, bytes, ctx->stream));
     ctx->stat_k = k2;
@@ -1155,7 +1156,7 @@ int shl_stats_allreduce(shl_ctx* ctx) {
 }
 int shl_stats_join(shl_ctx* ctx) {
     if (!ctx) return SHL_ERR_ARG;
-    for (int k = 0; k < 2; k++) CU(cudaStreamWaitEvent(ctx->stream, ctx->ev_stats_done[k], 0));
+    for (int k = 0; k < shl_ctx::kStatBufs; k++) CU(cudaStreamWaitEvent(ctx->stream, ctx->ev_stats_done[k], 0));
     return SHL_OK;
 }
 int shl_stats_fetch(shl_ctx* ctx, uint64_t* out, uint32_t n) {
