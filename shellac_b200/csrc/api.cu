@@ -264,6 +264,11 @@ static int ctx_setup(shl_ctx* ctx, int device) {
     shl_place_out& q = ctx->dq;
     CU(dalloc(&q.md5, 16 * n)); CU(dalloc(&q.hash, n)); CU(dalloc(&q.node, n));
     CU(dalloc(&ctx->d_ch_len, n)); CU(dalloc(&ctx->d_ch_size, n)); CU(dalloc(&ctx->d_ch_ok, n));
+    { const char* cv = getenv("SHL_CARVEOUT");      // percent of the SM's 228 KiB given to shared memory (default: the driver's choice)
+      if (cv && atoi(cv) > 0) {
+          CU(cudaFuncSetAttribute(shl::k_route<true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(cv)));
+          CU(cudaFuncSetAttribute(shl::k_route<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(cv)));
+      } }
     CU(cudaFuncSetAttribute(shl::k_route<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
     CU(cudaFuncSetAttribute(shl::k_route<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
     CU(cudaFuncSetAttribute(shl::k_route<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));

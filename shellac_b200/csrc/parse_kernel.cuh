@@ -414,6 +414,9 @@ __device__ __forceinline__ bm2 window_bits(const uint32_t c, const uint4& va, co
 }
 
 // bitmaps of span[0:nbytes) (A0 is 32-byte aligned, nbytes <= kSpanMax)
+#ifndef SHL_OPT_PREFETCH
+#define SHL_OPT_PREFETCH 0
+#endif
 #ifndef SHL_OPT_ROWS_NOALLOC
 #define SHL_OPT_ROWS_NOALLOC 0
 #endif
@@ -742,6 +745,12 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, SHL_OPT_MINBLOCKS) k_rout
                 coal = true;
                 s0 = (uint32_t)(m - A0);
                 if (have) bm_walk(bm, s0, L, gw);
+#if SHL_OPT_PREFETCH
+                // the epilogue touches every 128-byte line of the message again (first line, URL, value
+                // edges): ask for them now, while the first-line work covers the round trip
+                if (have && gw.T >= 0)
+                    for (int o = 0; o < gw.T + 4; o += 128) asm volatile("prefetch.global.L1 [%0];" ::"l"(m + o));
+#endif
                 sc.idx = gw.idx; sc.T = gw.T; sc.n_c = gw.n_c;
             }
         }
