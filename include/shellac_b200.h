@@ -111,7 +111,10 @@ typedef struct shl_parse_out {
     int64_t*  content_len;     /* HttpParser._content_len after the header state (0 if chunked)    */
     shl_hdr_span* hdr;         /* record arena, `hdr_cap` entries                                  */
     uint64_t  hdr_cap;
-    uint64_t* hdr_used;        /* one element: records written                                     */
+    uint64_t* hdr_used;        /* one element: records written.  The records of a message are contiguous
+                                * from hdr_base[i]; between messages the arena may have GAPS (the host-buffer
+                                * calls cut batches of >= 65 536 messages into chunks that each own a slice
+                                * of it): records in use end at max(hdr_base[i] + n_headers[i]), not at hdr_used */
     /* Optional (all four NULL / 0 = not wanted): the header NAMES lower-cased as the reference stores
      * them (key.lower(), HttpParser.py:330; ASCII only, like Python 2's str.lower()).  Message i's
      * names lie back to back, in record order, from lkeys[lkey_base[i]]: name k starts

@@ -88,3 +88,22 @@ def test_reactor_shim_on_device(golden):
         _scenario(EngineRouter(eng), golden)
     finally:
         eng.close()
+
+
+@pytest.mark.gpu
+def test_engine_router_large_batch_keeps_every_header():
+    """A batch of >= 65 536 messages takes the chunked host path, whose header records lie in per-chunk
+    slices of the arena: the router's detached copy must still hold the LAST chunk's records."""
+    from shellac_b200.batch import MessageView
+    from shellac_b200.engine import Engine
+    from shellac_b200.reactor import EngineRouter
+    eng = Engine(device=0, max_msgs=1 << 17, max_bytes=1 << 26)
+    eng.ring_build(HOSTS)
+    c2 = eng.corpus_host(20130725, 0, 70000, 0)
+    msgs = [c2.message(i) for i in range(70000)]
+    pout, qout, fout = EngineRouter(eng, msgs=1 << 17, nbytes=1 << 26).route(msgs)
+    o = O.orc_parse(Arena.pack(msgs))
+    for i in (0, 1, 34999, 65535, 65536, 69998, 69999):
+        got = MessageView(msgs[i], pout, i, fout).header_items()
+        assert got == MessageView(msgs[i], o, i).header_items() and len(got) >= 8, i
+    eng.close()
