@@ -68,7 +68,8 @@ struct shl_ctx {
     int sm_count = 148, grid_waves = 16;
     uint64_t launches = 0;
     // pipelined host-buffer path: chunks round-robin over these streams so H2D, kernel and D2H overlap
-    static constexpr int kPipe = 4, kMaxChunks = 16;
+    static constexpr int kPipe = 4, kMaxChunks = 64;
+    int chunk_msgs = 65536, max_chunks = 8;     // SHL_CHUNK_MSGS / SHL_MAX_CHUNKS: messages per chunk, chunks per batch
     cudaStream_t pipe[kPipe]{};
     cudaEvent_t ev_fork = nullptr, ev_join[kPipe]{}, ev_chunk[kMaxChunks]{};
     uint64_t* d_chunk_used = nullptr;     // [kMaxChunks]
@@ -280,6 +281,8 @@ static int ctx_setup(shl_ctx* ctx, int device) {
     CU(dalloc(&ctx->d_chunk_used, shl_ctx::kMaxChunks));
     CU(cudaHostAlloc(reinterpret_cast<void**>(&ctx->h_chunk_used), shl_ctx::kMaxChunks * sizeof(uint64_t), cudaHostAllocDefault));
     { const char* pl = getenv("SHL_PIPELINE"); if (pl && pl[0] == '0') ctx->pipeline = 0; }
+    { const char* cm = getenv("SHL_CHUNK_MSGS"); if (cm && atoi(cm) >= 1024) ctx->chunk_msgs = atoi(cm); }
+    { const char* mc = getenv("SHL_MAX_CHUNKS"); if (mc && atoi(mc) >= 2) ctx->max_chunks = atoi(mc); }
     { const char* sm = getenv("SHL_SMALL"); if (sm && sm[0] == '0') ctx->small_path = 0; }
     const char* fs = getenv("SHL_FORCE_SCALAR");
     ctx->force_scalar = (fs && fs[0] == '1') ? 1 : 0;
@@ -710,7 +713,7 @@ static int route_pipelined(shl_ctx* ctx, const uint8_t* arena, uint64_t arena_by
     if (!ctx->pipeline || !arena || n < 65536) return 1;
     ctx->cur_dp = ctx->dp; ctx->cur_n = n;
     if (qout) { ctx->cur_node = ctx->dq.node; ctx->cur_hist = qout->hist ? ctx->d_hist : nullptr; }
-    const int nch = (int)std::min<uint64_t>(kMaxChunks, std::max<uint64_t>(2, n / 65536));
+    const int nch = (int)std::min<uint64_t>((uint64_t)std::min(kMaxChunks, ctx->max_chunks), std::max<uint64_t>(2, n / (uint64_t)ctx->chunk_msgs));
     const uint64_t per = ((n + nch - 1) / nch + 31) & ~31ull;
     // cheap density probe (the exact byte range of a chunk is computed right before it is queued,
     // so the host scan of the index overlaps the copies of the previous chunks): the arena is
