@@ -617,6 +617,9 @@ def run_route(args):
         'metric': metric, 'value': value, 'unit': unit, 'n_gpus': world, 'steps': steps,
         'warmup': args.warmup, 'ms_per_step': ms / steps, 'higher_is_better': True,
         'scaling': 'weak' if cfg == 2 else 'strong', 'vs_baseline': None, 'dtype': 'u8', 'data': 'synthetic', 'config': conf,
+        'value_note': 'device-resident: the arena is already in HBM when the timed region starts (kernel + counter all-reduce); '
+                      'the end-to-end number through the C ABI with host buffers is `e2e`; vs_baseline stays null because the '
+                      'reference publishes no number for this metric (BASELINE.md)',
         'parallelism': 'dp%d (batch-sharded, no data-path collective; %d uint64 counters summed by the library\'s NCCL '
                        'all-reduce every %s step(s), overlapped with the next kernel)' % (world, n_stat, args.stats_every or 'K'),
         'mean_request_bytes': b0_bytes / m0, 'mean_header_lines': n_hdr / m0,
