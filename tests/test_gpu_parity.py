@@ -734,3 +734,46 @@ def test_compact_records_equal_the_wide_layout(eng, golden):
         class R: pass
         r = R(); r.n_headers, r.hdr_base, r.hdr = rec['n_headers'].astype(np.uint32), rec['hdr_base'], hdr
         assert (_records(r, n) == a).all()
+
+
+def test_mutated_corpus_messages(eng):
+    """Well-formed config-2 requests with a few bytes overwritten, inserted or deleted (CR, LF, ':', ' ',
+    tab, NUL, a letter): near-valid structure is what the bitmap path's alternation check, first-line
+    shortcut and value strip have to get right.  route (fused) vs the oracle, 3 seeds x 20 000 messages."""
+    hosts = ['10.0.0.%d' % (i + 1) for i in range(16)]
+    eng.ring_build(hosts)
+    vals, nodes = O.orc_ring(hosts, [11211] * 16)
+    c2 = eng.corpus_host(20130725, 200000, 20000, 0)
+    base = [c2.message(i) for i in range(20000)]
+    pool = [b'\r', b'\n', b':', b' ', b'\t', b'\x00', b'a', b'\r\n', b': ', b'  ', b'\r\n\r\n', b'']
+    seen = set()
+    for seed in (1, 2, 3):
+        rng = np.random.default_rng(seed)
+        msgs = []
+        for m in base:
+            b = bytearray(m)
+            for _ in range(int(rng.integers(0, 4))):
+                p = int(rng.integers(0, len(b) + 1))
+                t = pool[int(rng.integers(0, len(pool)))]
+                op = int(rng.integers(0, 3))
+                if op == 0:
+                    b[p:p + len(t)] = t                 # overwrite
+                elif op == 1:
+                    b[p:p] = t                          # insert
+                else:
+                    del b[p:p + int(rng.integers(1, 4))]   # delete
+            msgs.append(bytes(b))
+        ar = eng.pack(msgs)
+        n = ar.n
+        pg, qg = eng.route(ar)
+        o = O.orc_parse(ar)
+        assert_parse_equal(ar, pg, o, 'mutated seed %d' % seed)
+        st = o.status[:n]
+        r = ((st & N.F_MESSAGE_COMPLETE) != 0) & ((st & N.F_IS_REQUEST) != 0) & ((st & N.F_FIRST_LINE_DONE) != 0) & \
+            ((st & 0xff) == 0) & ((st & N.F_KEY_TOO_LONG) == 0)
+        koff = (ar.off + o.sp1[:n] + 1).astype(np.uint64); klen = (o.sp2[:n] - o.sp1[:n] - 1).astype(np.uint32)
+        koff[~r] = 0; klen[~r] = 0
+        oq = O.orc_place(ar, vals, nodes, 16, np.ascontiguousarray(koff), np.ascontiguousarray(klen))
+        assert (qg.node[:n][r] == oq.node[:n][r]).all() and (qg.node[:n][~r] == 0xffffffff).all()
+        seen |= set(int(c) for c in np.unique(st & 0xff))
+    assert {N.S_OK, N.S_INCOMPLETE_HEADERS, N.E_FIRSTLINE_PARTS, N.E_HDR_NO_SEP, N.E_HDR_MULTI_SEP} <= seen, seen
