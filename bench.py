@@ -923,6 +923,13 @@ def facade_rates(eng, ar, n=1 << 16):
     touched = sum(1 for p in ps[::16] if p.message_complete() and p.url() is not None and len(p.headers()) > 0)
     dt_touch = time.perf_counter() - t1
     assert touched == len(ps[::16])
+    t3 = time.perf_counter()
+    for m in msgs[:1000]:                       # the reference's own driving loop (test/HttpParserTests.py:36-39), one object per message
+        p, data = HttpParser(backend=be), m
+        while data and not p.message_complete():
+            c = p.parse(data, len(data))
+            data = data[c:]
+    dt_inc = time.perf_counter() - t3
     shim = ReactorShim(EngineRouter(eng, msgs=512, nbytes=1 << 19))
     for fd in range(512):
         shim.feed(fd, msgs[fd])
@@ -937,6 +944,7 @@ def facade_rates(eng, ar, n=1 << 16):
         assert len(done) == 512
     return {'parse_many_requests_per_s': n / dt, 'parse_many_n': n,
             'parse_many_then_touch_every_16th_us_per_touched': dt_touch / max(touched, 1) * 1e6,
+            'incremental_parse_us_per_message': dt_inc / 1000 * 1e6,
             'reactor_tick_512_requests_us': float(np.median(ticks)) * 1e6,
             'reactor_tick_us_per_request': float(np.median(ticks)) * 1e6 / 512,
             'note': 'host Python on one core + the device call; parser objects materialise their fields on first access'}

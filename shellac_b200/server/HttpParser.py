@@ -247,6 +247,7 @@ class HttpParser(object):
         had = len(self._buf)
         self._buf += data
         v = self._be().views([self._buf])[0]
+        self._seen = (self._buf, v)             # the device has tokenised these bytes: the header state may reuse it
         if v.code in (N.S_INCOMPLETE_LINE, N.S_EMPTY):
             return length                                                   # :156-157
         fl = int(v.p.first_line_len[0])
@@ -264,7 +265,13 @@ class HttpParser(object):
     def _parse_headers(self, data, length):
         had = len(self._buf)
         self._buf += data
-        v = self._be().views([self._line + self._buf])[0]
+        full = self._line + self._buf
+        seen = getattr(self, '_seen', None)
+        if seen is not None and seen[0] == full:        # the caller handed back the rest of what the first-line call saw:
+            v = seen[1]                                 # one device round trip per message instead of two
+        else:
+            v = self._be().views([full])[0]
+        self._seen = None
         if v.code == N.S_INCOMPLETE_HEADERS:
             return length                                                   # :177-178
         if v.code == N.E_LIB_HDR_TOO_LARGE:
